@@ -127,6 +127,8 @@ typedef struct lara_stats
 typedef struct lara_ctx lara_ctx;
 
 int          lara_gpu_version(void);
+/* number of visible CUDA devices (0 when there is no driver / device) */
+int          lara_gpu_visible_devices(void);
 /* n_devices==0 / device_ids==NULL -> current device only. */
 int          lara_gpu_create(lara_ctx ** ctx, lara_params const * params, int n_devices, int const * device_ids);
 void         lara_gpu_destroy(lara_ctx * ctx);

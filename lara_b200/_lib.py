@@ -99,6 +99,7 @@ _P = C.POINTER
 GPU_SYMBOLS = {
     "lara_params_default": (None, [_P(LaraParams)]),
     "lara_gpu_version": (C.c_int, []),
+    "lara_gpu_visible_devices": (C.c_int, []),
     "lara_gpu_create": (C.c_int, [_P(C.c_void_p), _P(LaraParams), C.c_int, _P(C.c_int)]),
     "lara_gpu_destroy": (None, [C.c_void_p]),
     "lara_gpu_last_error": (C.c_char_p, [C.c_void_p]),

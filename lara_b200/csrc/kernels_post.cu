@@ -1,0 +1,617 @@
+// kernels_post.cu -- everything of one subgradient iteration that follows the DP fill, one warp per pair:
+//
+//   traceback            SeqAn:align/dp_traceback_impl.h:190-418,456-546 + dp_algorithm_impl.h:1168-1185
+//   evaluateLines        src/lagrange.hpp:147-221
+//   valid_solution       src/lagrange.hpp:325-423
+//   greedy matching      src/matching.hpp:99-192 (lookahead-k with exact conflict resolution)
+//   bounds / step / dual src/subgradient_solver.hpp:247-286  (scalar build)
+//                        src/subgradient_solver_simd.hpp:292-350 (SIMD build, wrapping int32 step)
+//   updateScores         src/lagrange.hpp:312-323
+//   getStructureLines    src/lagrange.hpp:437-487
+//
+// The reference's per-edge std::set priority queues are not materialised: the top of queue l is
+// max_m key(l,m) (kept in pv[l]) with key(l,m) = seqScore(l) + struct(l,m) + dual(l->m), and its
+// iteration order among tied tops is ascending partner id (rows are stored in that order).
+#include "lara_gpu.cuh"
+
+namespace lara
+{
+
+namespace
+{
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kMaxLookahead = 8;
+
+// pair slots (x,y), x<y<8 in lexicographic order == order of the reference's conflicts vector
+__constant__ uint8_t cSlotX[28] = {0,0,0,0,0,0,0, 1,1,1,1,1,1, 2,2,2,2,2, 3,3,3,3, 4,4,4, 5,5, 6};
+__constant__ uint8_t cSlotY[28] = {1,2,3,4,5,6,7, 2,3,4,5,6,7, 3,4,5,6,7, 4,5,6,7, 5,6,7, 6,7, 7};
+
+__device__ __forceinline__ uint32_t involve_mask(int x)
+{
+    uint32_t m = 0;
+    #pragma unroll
+    for (int s = 0; s < 28; ++s)
+        if (cSlotX[s] == x || cSlotY[s] == x)
+            m |= 1u << s;
+    return m;
+}
+
+// Matching::solveConflicts (src/matching.hpp:99-141) on bit masks: conf = set of conflicting pair slots,
+// result = set of eliminated selection items.  In every conflict (first, second) the reference's edgeS is the
+// later queue entry (second) and edgeL the earlier one (first), because the selection is in queue order.
+__device__ uint32_t solve_conflicts(uint32_t conf, int32_t & weight, int32_t const * w, uint32_t const * inv)
+{
+    if (conf == 0u)
+        return 0u;
+    int const s = __ffs(conf) - 1;
+    int const edgeL = cSlotX[s], edgeS = cSlotY[s];
+    int32_t weightS = w[edgeS], weightL = w[edgeL];
+    if (__popc(conf) == 1)
+    {
+        weight += weightS;
+        return 1u << edgeS;
+    }
+    uint32_t const remS = conf & ~inv[edgeS];
+    uint32_t elimS = solve_conflicts(remS, weightS, w, inv);
+    if (weightS > weightL)
+    {
+        uint32_t const remL = conf & ~inv[edgeL];
+        if (remS != remL)
+        {
+            uint32_t elimL = solve_conflicts(remL, weightL, w, inv);
+            if (weightS > weightL)
+            {
+                weight += weightL;
+                return elimL | (1u << edgeL);
+            }
+        }
+    }
+    weight += weightS;
+    return elimS | (1u << edgeS);
+}
+
+struct WarpSmem
+{
+    int16_t * lineOfA;      // [maxLa]  line index of A position or -1
+    uint32_t * linesRev;    // [maxLb]  (a << 16) | b in traceback order (last line first)
+    int32_t * curE;         // [maxLb]  compact edge id per line (alignment order)
+    uint8_t * matched;      // [maxLb]
+    unsigned long long * cand;  // [smemCand]
+    int32_t * misc;         // [16]: 0 nList, 1 nCand, 2 matchScore, 3..10 selection weights, 11 error
+};
+
+__device__ __forceinline__ uint32_t trace_nibble(int32_t const * __restrict__ tr, int R, int W, int nSteps, int c, int r)
+{
+    int const k = (r - 1) / R, j = (r - 1) - k * R;
+    int const t = c - 1 + k;
+    int const wj = j >> 3;
+    int const nInWord = min(8, R - 8 * wj);
+    uint32_t const word = (uint32_t)tr[(size_t)k * ((size_t)nSteps * W) + (size_t)t * W + wj];
+    return (word >> (4 * (nInWord - 1 - (j & 7)))) & 15u;
+}
+
+// SeqAn trace byte of an inner cell from our nibble (SeqAn:align/dp_profile.h:125-134)
+__device__ __forceinline__ uint32_t seqan_tv(uint32_t nib)
+{
+    uint32_t tv = (nib & kTrGap) ? ((nib & kTrFromH) ? 32u : 64u) : 1u;
+    tv |= (nib & kTrVOpen) ? 16u : 4u;
+    tv |= (nib & kTrHOpen) ? 8u : 2u;
+    return tv;
+}
+
+// Traceback + evaluateLines by one thread.  Returns number of lines; lines in reverse order.
+__device__ int traceback_walk(PairDesc const & d, PairState const & st, int32_t const * __restrict__ arena,
+                              int32_t go, int32_t ge, uint32_t * linesRev, int32_t & gapOut)
+{
+    int32_t const * __restrict__ tr = arena + d.offTrace;
+    int const R = d.R, W = d.W, nSteps = d.nSteps;
+    int c = d.la, r = d.lb;
+    uint32_t tv = seqan_tv(trace_nibble(tr, R, W, nSteps, c, r));
+    // _correctTraceValue (dp_algorithm_impl.h:1168-1185) then _retrieveInitialTraceDirection
+    // (dp_traceback_impl.h:456-483, PreferGapsAtEnd_): gaps are preferred at the end cell on ties.
+    if (st.vEnd == st.sEnd) tv = (tv & (4u | 16u)) | 64u;
+    else if (st.hEnd == st.sEnd) tv = (tv & (2u | 8u)) | 32u;
+    else if (tv & 64u) tv &= (4u | 16u | 64u);
+    else if (tv & 32u) tv &= (2u | 8u | 32u);
+    int n = 0;
+    int32_t gap = 0;
+    int prev = 0;                       // 0 match, 1 vertical (gap in A), 2 horizontal (gap in B)
+    auto fetch = [&]() -> uint32_t { return (c > 0 && r > 0) ? seqan_tv(trace_nibble(tr, R, W, nSteps, c, r)) : 0u; };
+    auto stepV = [&]() { gap += (prev == 1) ? ge : go; prev = 1; --r; };
+    auto stepH = [&]() { gap += (prev == 2) ? ge : go; prev = 2; --c; };
+    while (c > 0 && r > 0)
+    {
+        if (tv & 1u)
+        {
+            --c; --r; prev = 0;
+            linesRev[n++] = ((uint32_t)c << 16) | (uint32_t)r;
+            tv = fetch();
+        }
+        else if ((tv & 64u) && (tv & 4u))
+        {
+            while ((tv & 4u) && r != 1) { stepV(); tv = fetch(); }
+            stepV(); tv = fetch();
+        }
+        else if ((tv & 64u) && (tv & 16u)) { stepV(); tv = fetch(); }
+        else if ((tv & 32u) && (tv & 2u))
+        {
+            while ((tv & 2u) && c != 1) { stepH(); tv = fetch(); }
+            stepH(); tv = fetch();
+        }
+        else if ((tv & 32u) && (tv & 8u)) { stepH(); tv = fetch(); }
+        else break;
+    }
+    while (r > 0) stepV();              // leading gaps (dp_traceback_impl.h:541-544)
+    while (c > 0) stepH();
+    gapOut = gap;
+    return n;
+}
+
+__device__ __forceinline__ int32_t warp_sum(int32_t v)
+{
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    return v;
+}
+__device__ __forceinline__ int32_t warp_min(int32_t v)
+{
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(kFull, v, o));
+    return v;
+}
+__device__ __forceinline__ int32_t warp_max(int32_t v)
+{
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(kFull, v, o));
+    return v;
+}
+
+// bitonic sort of P (power of two) 64-bit keys by one warp
+__device__ void warp_bitonic_sort(unsigned long long * buf, int P, int lane)
+{
+    for (int k = 2; k <= P; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1)
+        {
+            for (int i = lane; i < P; i += 32)
+            {
+                int const ixj = i ^ j;
+                if (ixj > i)
+                {
+                    unsigned long long a = buf[i], b = buf[ixj];
+                    bool const asc = (i & k) == 0;
+                    if ((a > b) == asc) { buf[i] = b; buf[ixj] = a; }
+                }
+            }
+            __syncwarp();
+        }
+}
+
+// Matching::computeGreedyMatching (src/matching.hpp:143-192) over K sorted candidates.
+// key = [~(sc ^ 0x80000000) : 32][line index l : 16][line index r : 16]  (ascending == queue order
+// (-2*sc, lineL, lineR) because line indices grow with the edge ids).
+__device__ int32_t greedy_matching(unsigned long long const * keys, int K, int lookahead, uint8_t * matched,
+                                   int32_t * misc, int lane)
+{
+    int L = lookahead;
+    if (L > K) L = K; else if (L == 0) L = 5;                  // :153-156
+    uint32_t inv[kMaxLookahead];
+    #pragma unroll
+    for (int x = 0; x < kMaxLookahead; ++x) inv[x] = involve_mask(x);
+    int32_t score = 0;
+    int pos = 0;
+    while (pos < K)
+    {
+        // selection: the next L candidates whose endpoints are both unmatched (:165-167)
+        int ns = 0;
+        int mySel = -1;
+        while (ns < L && pos < K)
+        {
+            int const i = pos + lane;
+            bool ok = false;
+            if (i < K)
+            {
+                unsigned long long const key = keys[i];
+                ok = !matched[(key >> 16) & 0xffffu] && !matched[key & 0xffffu];
+            }
+            unsigned const bal = __ballot_sync(kFull, ok);
+            int const have = __popc(bal), need = L - ns;
+            int const take = min(have, need);
+            if (lane >= ns && lane < ns + take)
+                mySel = pos + (int)__fns(bal, 0, lane - ns + 1);
+            if (have >= need)
+                pos = pos + (int)__fns(bal, 0, need) + 1;
+            else
+                pos = min(pos + 32, K);
+            ns += take;
+        }
+        // my selected interaction
+        int32_t w = 0;
+        int il = -1, ir = -2;
+        if (lane < ns)
+        {
+            unsigned long long const key = keys[mySel];
+            uint32_t const hi = (uint32_t)(key >> 32);
+            int32_t const sc = (int32_t)((~hi) ^ 0x80000000u);
+            w = 2 * sc;                                         // -get<0>(interaction)
+            il = (int)((key >> 16) & 0xffffu);
+            ir = (int)(key & 0xffffu);
+            misc[3 + lane] = w;
+        }
+        __syncwarp();
+        // conflicts (:170-174): lane s tests pair slot s
+        bool cf = false;
+        if (lane < 28)
+        {
+            int const x = cSlotX[lane], y = cSlotY[lane];
+            int const lx = __shfl_sync(0x0fffffffu, il, x), rx = __shfl_sync(0x0fffffffu, ir, x);
+            int const ly = __shfl_sync(0x0fffffffu, il, y), ry = __shfl_sync(0x0fffffffu, ir, y);
+            cf = (y < ns) && (lx == ly || lx == ry || rx == ly || rx == ry);
+        }
+        uint32_t const conf = __ballot_sync(kFull, cf);
+        uint32_t elim = 0;
+        if (conf)
+        {
+            if (lane == 0)
+            {
+                int32_t weight = 0;
+                elim = solve_conflicts(conf, weight, misc + 3, inv);
+            }
+            elim = __shfl_sync(kFull, elim, 0);
+        }
+        // commit (:181-189)
+        int32_t add = 0;
+        if (lane < ns && !((elim >> lane) & 1u))
+        {
+            matched[il] = 1;
+            matched[ir] = 1;
+            add = w;
+        }
+        score += warp_sum(add);
+        __syncwarp();
+    }
+    return score;
+}
+
+__device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b)
+{
+    uint32_t const * bits = (uint32_t const *)(arena + d.offBits) + (size_t)a * d.bitWords;
+    int e = arena[d.offRowStart + a];
+    int const wb = b >> 5;
+    for (int w = 0; w < wb; ++w) e += __popc(bits[w]);
+    uint32_t const word = bits[wb];
+    if (!((word >> (b & 31)) & 1u)) return -1;
+    return e + __popc(word & ((1u << (b & 31)) - 1u));
+}
+
+template <bool kTracebackOnly>
+__global__ void __launch_bounds__(128)
+iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
+                    int32_t * __restrict__ arena, DevParams P, PairOutHdr * __restrict__ outHdr,
+                    int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
+                    int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand)
+{
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    int const warpInBlock = threadIdx.x >> 5;
+    int const lane = threadIdx.x & 31;
+    int const p = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
+    if (p >= n)
+        return;
+    PairState & st = state[p];
+    if (st.done)
+        return;
+    PairDesc const & d = desc[p];
+
+    // carve the per-warp shared memory
+    size_t const candBytes = (size_t)smemCand * 8;
+    size_t const perWarp = candBytes + 64 + (size_t)maxLb * 8 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    unsigned char * base = smemRaw + (size_t)warpInBlock * perWarp;
+    WarpSmem sm;
+    sm.cand = (unsigned long long *)base;                     base += candBytes;
+    sm.misc = (int32_t *)base;                                base += 64;
+    sm.linesRev = (uint32_t *)base;                           base += (size_t)maxLb * 4;
+    sm.curE = (int32_t *)base;                                base += (size_t)maxLb * 4;
+    sm.lineOfA = (int16_t *)base;                             base += ((size_t)maxLa * 2 + 15) / 16 * 16;
+    sm.matched = (uint8_t *)base;
+
+    int const la = d.la, lb = d.lb;
+    (void)lb;
+
+    // ---- 1. traceback + evaluateLines ------------------------------------------------------------
+    int nLines = 0;
+    int32_t gapScore = 0;
+    if (lane == 0)
+    {
+        nLines = traceback_walk(d, st, arena, P.go, P.ge, sm.linesRev, gapScore);
+        sm.misc[0] = 0; sm.misc[1] = 0; sm.misc[2] = 0; sm.misc[11] = 0;
+    }
+    nLines = __shfl_sync(kFull, nLines, 0);
+    gapScore = __shfl_sync(kFull, gapScore, 0);
+    for (int a = lane; a < la; a += 32) sm.lineOfA[a] = -1;
+    __syncwarp();
+    if (kTracebackOnly)
+    {
+        // unit entry point: lines in alignment order to offLines, count and gap score to the state
+        for (int i = lane; i < nLines; i += 32)
+            arena[d.offLines + i] = (int32_t)sm.linesRev[nLines - 1 - i];
+        if (lane == 0) { st.nLines = nLines; st.gapScore = gapScore; }
+        return;
+    }
+
+    int32_t const * __restrict__ seqScore = arena + d.offSeqScore;
+    int32_t * __restrict__ pv = arena + d.offPv;
+    int32_t const * __restrict__ ioff = arena + d.offIoff;
+    int32_t const * __restrict__ part = arena + d.offPart;
+    int32_t const * __restrict__ ppos = arena + d.offPpos;
+    int32_t const * __restrict__ sc = arena + d.offSc;
+    int32_t * __restrict__ dual = arena + d.offDual;
+    int32_t const * __restrict__ rev = arena + d.offRev;
+    int32_t * __restrict__ list = arena + d.offList;
+    bool const candInSmem = d.kCap <= smemCand;
+    unsigned long long * cand = candInSmem ? sm.cand : (unsigned long long *)(arena + d.offCand);
+
+    // ---- 2. lines -> edge ids --------------------------------------------------------------------
+    for (int i = lane; i < nLines; i += 32)
+    {
+        uint32_t const ab = sm.linesRev[nLines - 1 - i];
+        int const a = (int)(ab >> 16), b = (int)(ab & 0xffffu);
+        sm.lineOfA[a] = (int16_t)i;
+        int const e = edge_of(d, arena, a, b);
+        if (e < 0) sm.misc[11] = 1;            // "Alignment match where no alignment edge is defined!"
+        sm.curE[i] = e;
+        sm.matched[i] = 0;
+    }
+    __syncwarp();
+
+    // ---- 3. subgradient marks, sequence part of the lower bound, matching candidates (:343-391) ----
+    int32_t lbSeq = 0;
+    for (int i = lane; i < nLines; i += 32)
+    {
+        int const e = sm.curE[i];
+        if (e < 0) continue;
+        int32_t const sq = seqScore[e];
+        int32_t const top = pv[e];
+        lbSeq += sq;
+        for (int x = ioff[e]; x < ioff[e + 1]; ++x)
+        {
+            int const m = part[x];
+            uint32_t const pp = (uint32_t)ppos[x];
+            int const li = sm.lineOfA[pp >> 16];
+            bool const inSol = li >= 0 && (sm.linesRev[nLines - 1 - li] & 0xffffu) == (pp & 0xffffu);
+            int32_t const s = sc[x];
+            if (sq + s + dual[x] == top)
+            {
+                bool cycle = false;
+                int const rx = rev[x];
+                if (inSol)
+                    cycle = (seqScore[m] + s + dual[rx] == pv[m]);
+                if (!cycle)
+                {
+                    int const at = atomicAdd(&sm.misc[0], 2);
+                    list[at] = x;                                   // subgradient +1
+                    list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
+                }
+            }
+            if (inSol && e < m)
+            {
+                int const at = atomicAdd(&sm.misc[1], 1);
+                unsigned long long const key =
+                    ((unsigned long long)(~((uint32_t)s ^ 0x80000000u)) << 32) | ((unsigned long long)i << 16) | (unsigned long long)li;
+                if (at < d.kCap) cand[at] = key; else sm.misc[11] = 2;
+            }
+        }
+    }
+    lbSeq = warp_sum(lbSeq);
+    __syncwarp();
+    int const nList = sm.misc[0];
+    int const nCand = min(sm.misc[1], d.kCap);
+
+    // ---- 4. structural part of the lower bound ---------------------------------------------------
+    int32_t lbStruct = 0;
+    if (nList > 0)
+    {
+        int Pn = 32;
+        while (Pn < nCand) Pn <<= 1;
+        for (int i = nCand + lane; i < Pn; i += 32) cand[i] = ~0ull;
+        __syncwarp();
+        if (nCand > 1) warp_bitonic_sort(cand, Pn, lane);
+        lbStruct = greedy_matching(cand, nCand, P.lookahead, sm.matched, sm.misc, lane);
+    }
+    else
+    {
+        // every top is part of a cycle (:397-409): add the structure score of the first tied top
+        int32_t add = 0;
+        for (int i = lane; i < nLines; i += 32)
+        {
+            int const e = sm.curE[i];
+            if (e < 0) continue;
+            int32_t const sq = seqScore[e], top = pv[e];
+            int found = -1;
+            bool selfFirst = false;
+            for (int x = ioff[e]; x < ioff[e + 1] && found < 0 && !selfFirst; ++x)
+            {
+                if (part[x] > e && sq == top) { selfFirst = true; break; }
+                if (sq + sc[x] + dual[x] == top) found = x;
+            }
+            if (found >= 0 && !selfFirst)
+            {
+                add += sc[found];
+                sm.matched[i] = 1;
+                int const li = sm.lineOfA[(uint32_t)ppos[found] >> 16];
+                if (li >= 0) sm.matched[li] = 1;
+            }
+        }
+        lbStruct = warp_sum(add);
+    }
+    __syncwarp();
+
+    // ---- 5. primal value, best structural alignment (:412-421) -----------------------------------
+    int32_t const primal = lbSeq + lbStruct + gapScore;
+    bool const improved = primal > st.bestScore;
+    if (improved)
+    {
+        for (int i = lane; i < nLines; i += 32)
+            arena[d.offBest + i] = (int32_t)(sm.linesRev[nLines - 1 - i] | (sm.matched[i] ? 0x80000000u : 0u));
+    }
+
+    // ---- 6. bounds, step size, termination (solver :247-286 / simd :292-350) ----------------------
+    float stepSize = 0.f;
+    int finished = 0;
+    if (lane == 0)
+    {
+        if (improved) { st.bestScore = primal; st.nBest = nLines; }
+        int32_t bestUpper = st.bestUpper, bestLower = st.bestLower;
+        uint32_t nd = st.nondecreasing;
+        int32_t const cu = st.currentUpper;
+        st.currentLower = primal;
+        if (cu < bestUpper) { bestUpper = cu; nd = 0; }
+        if (primal > bestLower) { bestLower = primal; nd = 0; }
+        if (P.stepMode == LARA_STEP_SCALAR_FLOAT)
+        {
+            float f = st.stepFactorF;
+            if (nd++ >= (uint32_t)P.maxNondecreasing) { f = __fdiv_rn(f, 2.0f); nd = 0; }
+            st.stepFactorF = f;
+            stepSize = __fdiv_rn(__fmul_rn(f, __int2float_rn(bestUpper - bestLower)), __int2float_rn(nList));
+        }
+        else
+        {
+            int32_t f = st.stepFactorI;
+            nd += 1;
+            if (nd > (uint32_t)P.maxNondecreasing) { f = f / 2; nd = 0; }
+            st.stepFactorI = f;
+            int32_t const prod = (int32_t)((uint32_t)f * (uint32_t)(bestUpper - bestLower));
+            stepSize = __fdiv_rn(__fdiv_rn(__int2float_rn(prod), LARA_FACTOR2INT), __int2float_rn(nList));
+        }
+        st.bestUpper = bestUpper; st.bestLower = bestLower; st.nondecreasing = nd;
+        st.nLines = nLines; st.gapScore = gapScore; st.nList = nList;
+        st.remaining -= 1;
+        finished = (bestUpper == bestLower || st.remaining == 0) ? 1 : 0;
+        if (sm.misc[11]) st.error = sm.misc[11];
+    }
+    stepSize = __shfl_sync(kFull, stepSize, 0);
+    finished = __shfl_sync(kFull, finished, 0);
+
+    // ---- 7. multiplier update (:267-271) -----------------------------------------------------------
+    for (int i = lane; i < nList; i += 32)
+    {
+        uint32_t const x = (uint32_t)list[i];
+        int const di = (int)(x & 0x7fffffffu);
+        float const f = __int2float_rn(dual[di]);
+        dual[di] = __float2int_rz((x >> 31) ? __fadd_rn(f, stepSize) : __fsub_rn(f, stepSize));
+    }
+    __syncwarp();
+
+    if (!finished)
+    {
+        // ---- 8a. updateScores (:312-323): refresh the queue top of every touched edge -------------
+        int32_t * __restrict__ vals = arena + d.offVals;
+        int32_t const * __restrict__ perm = arena + d.offPerm;
+        for (int i = lane; i < nList; i += 32)
+        {
+            int const di = (int)((uint32_t)list[i] & 0x7fffffffu);
+            int const l = part[rev[di]];                    // owner of interaction di
+            int32_t const sq = seqScore[l];
+            int32_t top = sq;
+            for (int x = ioff[l]; x < ioff[l + 1]; ++x)
+                top = max(top, sq + sc[x] + dual[x]);
+            pv[l] = top;
+            vals[perm[l]] = top;
+        }
+        return;
+    }
+
+    // ---- 8b. finished: getStructureLines (:437-487) -> result slot ---------------------------------
+    __syncwarp();
+    int const nBest = __shfl_sync(kFull, lane == 0 ? st.nBest : 0, 0);
+    int32_t minScore = 0, maxScore = 0;
+    float div = 0.f;
+    if (P.libLinear)
+    {
+        // minmax over ALL lenA*lenB queues (:445-448); an inactive edge's empty std::set reads as 0 there
+        int32_t mn = INT32_MAX, mx = INT32_MIN;
+        for (int e = lane; e < d.E; e += 32) { mn = min(mn, pv[e]); mx = max(mx, pv[e]); }
+        if ((int64_t)d.E < (int64_t)d.la * d.lb) { mn = min(mn, 0); mx = max(mx, 0); }
+        minScore = warp_min(mn);
+        maxScore = warp_max(mx);
+        div = __fdiv_rn(__fmul_rn(1.f, __uint2float_rn(P.libMax - P.libMin)), __int2float_rn(maxScore - minScore));
+    }
+    bool const swapIdx = d.seqFirst > d.seqSecond;
+    int32_t * __restrict__ out = outLines + outOff[p];
+    for (int i = lane; i < nBest; i += 32)
+    {
+        uint32_t const v = (uint32_t)arena[d.offBest + i];
+        int const a = (int)((v >> 16) & 0x7fffu), b = (int)(v & 0xffffu);
+        uint32_t const isMatched = v >> 31;
+        uint32_t w;
+        if (P.libLinear)
+        {
+            int const e = edge_of(d, arena, a, b);
+            unsigned long long const prod = (unsigned long long)isMatched * (unsigned long long)(long long)(pv[e] - minScore);
+            int32_t const val = __float2int_rz(__fmul_rn(__ull2float_rn(prod), div));
+            w = P.libMin + (uint32_t)val;
+        }
+        else
+            w = isMatched * 500u + 500u;
+        out[i] = swapIdx ? b : a;
+        out[d.lb + i] = swapIdx ? a : b;
+        out[2 * d.lb + i] = (int32_t)w;
+    }
+    if (lane == 0)
+    {
+        PairOutHdr h;
+        h.bestLower = st.bestLower; h.bestUpper = st.bestUpper;
+        h.iterations = P.numIterations - st.remaining; h.nLines = nBest;
+        outHdr[p] = h;
+        st.done = 1;
+        atomicSub(activeCount, 1);
+    }
+}
+
+size_t post_smem_per_warp(int maxLa, int maxLb, int smemCand)
+{
+    return (size_t)smemCand * 8 + 64 + (size_t)maxLb * 8 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+}
+
+} // namespace
+
+// opt in to the full shared memory carve-out for both instantiations (per device, at context creation)
+cudaError_t post_configure_device()
+{
+    int dev = 0, maxOptin = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    e = cudaDeviceGetAttribute(&maxOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(iterate_post_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(iterate_post_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
+}
+
+cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
+                                DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
+                                int32_t * activeCount, int maxLa, int maxLb, int smemCand, cudaStream_t stream)
+{
+    if (n <= 0) return cudaSuccess;
+    int const warpsPerBlock = 4;
+    size_t const smem = post_smem_per_warp(maxLa, maxLb, smemCand) * warpsPerBlock;
+    int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
+    iterate_post_kernel<false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, outHdr, outLines,
+                                                                             outOff, activeCount, maxLa, maxLb, smemCand);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * state, int32_t * arena,
+                                  int32_t go, int32_t ge, int maxLa, int maxLb, cudaStream_t stream)
+{
+    if (n <= 0) return cudaSuccess;
+    int const warpsPerBlock = 4;
+    size_t const smem = post_smem_per_warp(maxLa, maxLb, 0) * warpsPerBlock;
+    DevParams P{};
+    P.go = go; P.ge = ge;
+    int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
+    iterate_post_kernel<true><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, nullptr, nullptr,
+                                                                            nullptr, nullptr, maxLa, maxLb, 0);
+    return cudaGetLastError();
+}
+
+} // namespace lara

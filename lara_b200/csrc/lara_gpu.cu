@@ -1,0 +1,909 @@
+// lara_gpu.cu -- C ABI (include/lara_b200.h) and host orchestration of the GPU hot path.
+//
+// Drop-in seam: lara::solve(results, store, params)  (src/subgradient_solver.hpp:110, src/lara.cpp:57).
+// The reference keeps `threads` solver slots alive and refills them from a longest-first queue
+// (src/subgradient_solver.hpp:112-120, 286-325).  Here the queue becomes length-sorted BATCHES of pairs
+// that iterate in lock step; each iteration is one DP launch per rows-per-lane class plus one
+// post-processing launch.  Pairs are independent, so several GPUs simply take interleaved shares of the
+// sorted pair list (one host thread per device, no collective).
+#include "lara_gpu.cuh"
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <stdexcept>
+#include <tuple>
+#include <string>
+#include <thread>
+#include <vector>
+
+using namespace lara;
+
+namespace
+{
+
+thread_local std::string g_createErr;
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            throw std::runtime_error(std::string(#call) + ": " + cudaGetErrorString(e_));          \
+    } while (0)
+
+struct OrientedPair
+{
+    int32_t first, second;      // first = longer sequence (ties: lower index), like solver :117-120
+    int32_t la, lb;
+    int64_t request;            // position in the caller's pair list
+};
+
+// All device-side resources of one GPU.
+struct Device
+{
+    int id = 0;
+    cudaStream_t stream = nullptr;
+    DevInputs in{};
+    void * dSeq = nullptr, * dSeqOff = nullptr, * dBpPartner = nullptr, * dBpWeight = nullptr, * dBpOff = nullptr;
+    int32_t * negBuf = nullptr;
+    int32_t * dActive = nullptr;
+    int32_t * hActive = nullptr;            // pinned
+    std::vector<cudaEvent_t> events;
+    // share of the prepared pair list and its device-resident outputs
+    std::vector<OrientedPair> pairs;
+    PairOutHdr * dOutHdr = nullptr;
+    int32_t * dOutLines = nullptr;
+    int64_t * dOutOff = nullptr;
+    std::vector<int64_t> outOff;
+    int64_t outLinesTotal = 0;
+    lara_stats stats{};
+    std::string err;
+};
+
+} // namespace
+
+struct lara_ctx
+{
+    lara_params P{};
+    DevParams dp{};
+    std::string err;
+    std::vector<Device> devs;
+    // host copy of the inputs (for pair orientation and batch sizing)
+    int32_t nSeq = 0;
+    std::vector<int64_t> seqOff, bpOff;
+    std::vector<int32_t> nbp;               // base pairs per sequence
+    int64_t nPrepared = 0;
+    bool prepared = false, ran = false;
+    lara_stats stats{};
+    size_t batchPairsCap = 0;               // test hook: max pairs per batch (0 = automatic)
+};
+
+namespace
+{
+
+struct ResultOwner
+{
+    std::vector<lara_pair_result> pairs;
+    std::vector<int32_t> posLow, posHigh;
+    std::vector<uint32_t> weight;
+};
+
+DevParams make_dev_params(lara_params const & P)
+{
+    DevParams d{};
+    d.numIterations = P.num_iterations;
+    d.maxNondecreasing = P.max_nondecreasing;
+    d.lookahead = P.matching;
+    d.stepMode = P.step_mode;
+    d.stepSizeFactor = P.step_size_factor;
+    d.balance = P.balance;
+    d.sequenceScale = P.sequence_scale;
+    d.subopt = (int32_t)(P.suboptimal_diff * LARA_FACTOR2INT);      // src/lagrange.hpp:251
+    d.go = P.gap_open;
+    d.ge = P.gap_extend;
+    for (int i = 0; i < 25; ++i) d.tab[i] = P.score_matrix[i];
+    d.libMin = P.lib_score_min;
+    d.libMax = P.lib_score_max;
+    d.libLinear = P.lib_score_linear;
+    return d;
+}
+
+inline int64_t align4(int64_t x) { return (x + 3) & ~(int64_t)3; }
+
+// Bump allocator over one device allocation; offsets are relative to the batch's base pointer (in ints).
+struct Region
+{
+    int32_t * ptr = nullptr;
+    int64_t size = 0, used = 0;
+    int64_t baseDelta = 0;                  // (ptr - arenaBase) in ints
+    int64_t take(int64_t nInts)
+    {
+        int64_t const o = used;
+        used += align4(std::max<int64_t>(nInts, 1));
+        return baseDelta + o;
+    }
+};
+
+void device_free_inputs(Device & dv)
+{
+    cudaFree(dv.dSeq); cudaFree(dv.dSeqOff); cudaFree(dv.dBpPartner); cudaFree(dv.dBpWeight); cudaFree(dv.dBpOff);
+    dv.dSeq = dv.dSeqOff = dv.dBpPartner = dv.dBpWeight = dv.dBpOff = nullptr;
+}
+
+void device_free_outputs(Device & dv)
+{
+    cudaFree(dv.dOutHdr); cudaFree(dv.dOutLines); cudaFree(dv.dOutOff);
+    dv.dOutHdr = nullptr; dv.dOutLines = nullptr; dv.dOutOff = nullptr;
+}
+
+double ev_ms(cudaEvent_t a, cudaEvent_t b)
+{
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, a, b);
+    return (double)ms;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// One batch: pairs [begin, end) of dv.pairs (already length sorted).
+// ---------------------------------------------------------------------------------------------------
+void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
+{
+    int const n = (int)(end - begin);
+    DevParams const & dp = ctx.dp;
+    cudaStream_t const s = dv.stream;
+    std::vector<PairDesc> desc((size_t)n);
+    int maxLa = 0, maxLb = 0, maxK = 0;
+    // ---- stage A layout: everything that only depends on the lengths -----------------------------
+    int64_t sizeA = 0;
+    auto layoutA = [&](bool commit, Region & rg)
+    {
+        for (int i = 0; i < n; ++i)
+        {
+            OrientedPair const & op = dv.pairs[begin + i];
+            PairDesc & d = desc[(size_t)i];
+            if (!commit)
+            {
+                std::memset(&d, 0, sizeof(d));
+                d.la = op.la; d.lb = op.lb; d.seqFirst = op.first; d.seqSecond = op.second;
+                d.R = (op.lb + 31) / 32;
+                d.W = d.R <= 8 ? 1 : (d.R <= 16 ? 2 : 4);
+                d.nSteps = (op.la + 31 + 3) & ~3;
+                d.bitWords = (op.lb + 31) / 32;
+                d.kCap = std::min(ctx.nbp[op.first], ctx.nbp[op.second]) + 1;
+                maxLa = std::max(maxLa, d.la); maxLb = std::max(maxLb, d.lb); maxK = std::max(maxK, d.kCap);
+            }
+            int64_t const nFlagWords = (d.nSteps + 31) / 32;
+            d.offBits = rg.take((int64_t)d.la * d.bitWords);
+            d.offRowStart = rg.take(d.la + 1);
+            d.offFlags = rg.take(32 * nFlagWords);
+            d.offLanePtr = rg.take(32);
+            d.offTrace = rg.take(32ll * d.nSteps * d.W);
+            d.offLines = rg.take(d.lb);
+            d.offBest = rg.take(d.lb);
+            d.offCand = rg.take(2ll * d.kCap);
+            d.offScratch = rg.take((int64_t)d.la * d.lb + 6ll * (d.la + 1));
+        }
+    };
+    {
+        Region probe;
+        layoutA(false, probe);
+        sizeA = probe.used;
+    }
+    Region rA;
+    CK(cudaMallocAsync((void **)&rA.ptr, (size_t)sizeA * 4, s));
+    rA.size = sizeA;
+    int32_t * const arena = rA.ptr;
+    layoutA(true, rA);
+
+    PairDesc * dDesc = nullptr;
+    PairState * dState = nullptr;
+    CK(cudaMallocAsync((void **)&dDesc, sizeof(PairDesc) * (size_t)n, s));
+    CK(cudaMallocAsync((void **)&dState, sizeof(PairState) * (size_t)n, s));
+    CK(cudaMemsetAsync(dState, 0, sizeof(PairState) * (size_t)n, s));
+    CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
+
+    cudaEvent_t evS0 = dv.events[0], evS1 = dv.events[1];
+    CK(cudaEventRecord(evS0, s));
+    // ---- stage 1: edge filter -> E ------------------------------------------------------------------
+    CK(launch_edge_filter(n, dDesc, dState, arena, dv.in, dp, s));
+    CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    dv.stats.kernel_launches += 1;
+    // ---- stage B layout: per-edge arrays ---------------------------------------------------------------
+    int64_t sizeB = 0;
+    for (int i = 0; i < n; ++i) sizeB += 4 * align4(std::max(desc[(size_t)i].E, 1)) + align4(desc[(size_t)i].E + 1);
+    Region rB;
+    CK(cudaMallocAsync((void **)&rB.ptr, (size_t)sizeB * 4, s));
+    rB.size = sizeB; rB.baseDelta = rB.ptr - arena;
+    for (int i = 0; i < n; ++i)
+    {
+        PairDesc & d = desc[(size_t)i];
+        d.offCell = rB.take(d.E); d.offSeqScore = rB.take(d.E); d.offPv = rB.take(d.E); d.offPerm = rB.take(d.E);
+        d.offIoff = rB.take(d.E + 1);
+    }
+    CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
+    // ---- stage 2: counts -> D, nVals -----------------------------------------------------------------------
+    CK(launch_setup_count(n, dDesc, dState, arena, dv.in, dp, s));
+    CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    dv.stats.kernel_launches += 1;
+    int64_t sizeC = 0;
+    for (int i = 0; i < n; ++i) sizeC += 6 * align4(std::max(desc[(size_t)i].D, 1)) + align4(std::max(desc[(size_t)i].nVals, 1));
+    Region rC;
+    CK(cudaMallocAsync((void **)&rC.ptr, (size_t)sizeC * 4, s));
+    rC.size = sizeC; rC.baseDelta = rC.ptr - arena;
+    for (int i = 0; i < n; ++i)
+    {
+        PairDesc & d = desc[(size_t)i];
+        d.offPart = rC.take(d.D); d.offPpos = rC.take(d.D); d.offSc = rC.take(d.D); d.offDual = rC.take(d.D);
+        d.offRev = rC.take(d.D); d.offList = rC.take(d.D); d.offVals = rC.take(d.nVals);
+        dv.stats.n_active_edges += d.E; dv.stats.n_interactions += d.D;
+        dv.stats.filter_cells += 2ll * d.la * d.lb;
+    }
+    CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
+    // ---- stage 3: fill ---------------------------------------------------------------------------------------
+    CK(launch_setup_fill(n, dDesc, dState, arena, dv.in, dp, s));
+    dv.stats.kernel_launches += 1;
+    CK(cudaEventRecord(evS1, s));
+
+    // ---- rows-per-lane classes for the DP launches -------------------------------------------------------------
+    std::map<int, std::vector<int32_t>> classes;
+    for (int i = 0; i < n; ++i) classes[desc[(size_t)i].R].push_back(i);
+    std::vector<int32_t> idxAll;
+    std::vector<std::tuple<int, int, int>> cls;        // R, offset, count
+    for (auto & kv : classes)
+    {
+        cls.emplace_back(kv.first, (int)idxAll.size(), (int)kv.second.size());
+        idxAll.insert(idxAll.end(), kv.second.begin(), kv.second.end());
+    }
+    int32_t * dIdx = nullptr;
+    CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * idxAll.size(), s));
+    CK(cudaMemcpyAsync(dIdx, idxAll.data(), sizeof(int32_t) * idxAll.size(), cudaMemcpyHostToDevice, s));
+    *dv.hActive = n;
+    CK(cudaMemcpyAsync(dv.dActive, dv.hActive, sizeof(int32_t), cudaMemcpyHostToDevice, s));
+
+    // shared memory candidates: as many as fit next to the line arrays (cap 2048)
+    int smemCand = 32;
+    while (smemCand < maxK && smemCand < 2048) smemCand <<= 1;
+
+    // ---- the subgradient loop -------------------------------------------------------------------------------------
+    int const nIter = ctx.P.num_iterations;
+    size_t const needEv = 2 + 3 * (size_t)nIter;
+    while (dv.events.size() < needEv)
+    {
+        cudaEvent_t e;
+        CK(cudaEventCreate(&e));
+        dv.events.push_back(e);
+    }
+    int itersRun = 0;
+    int nextPoll = 1;
+    for (int it = 0; it < nIter; ++it)
+    {
+        CK(cudaEventRecord(dv.events[2 + 3 * (size_t)it], s));
+        for (auto const & c : cls)
+        {
+            CK(launch_gotoh_fill(std::get<0>(c), std::get<2>(c), dIdx + std::get<1>(c), dDesc, dState, arena, dv.negBuf,
+                                 dp.go, dp.ge, s));
+            dv.stats.kernel_launches += 1; dv.stats.dp_launches += 1;
+        }
+        CK(cudaEventRecord(dv.events[2 + 3 * (size_t)it + 1], s));
+        CK(launch_iterate_post(n, dDesc, dState, arena, dp, dv.dOutHdr + begin, dv.dOutLines, dv.dOutOff + begin,
+                               dv.dActive, maxLa, maxLb, smemCand, s));
+        dv.stats.kernel_launches += 1;
+        CK(cudaEventRecord(dv.events[2 + 3 * (size_t)it + 2], s));
+        itersRun = it + 1;
+        if (it + 1 == nextPoll && it + 1 < nIter)
+        {
+            CK(cudaMemcpyAsync(dv.hActive, dv.dActive, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            if (*dv.hActive <= 0) break;
+            nextPoll = nextPoll < 16 ? nextPoll * 2 : nextPoll + 16;
+        }
+    }
+    // error flags
+    std::vector<PairState> hState((size_t)n);
+    CK(cudaMemcpyAsync(hState.data(), dState, sizeof(PairState) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    for (int i = 0; i < n; ++i)
+    {
+        if (hState[(size_t)i].error)
+            throw std::runtime_error("internal invariant violated on the device (code " +
+                                     std::to_string(hState[(size_t)i].error) + ")");
+        if (!hState[(size_t)i].done)
+            throw std::runtime_error("pair did not finish within numIterations");
+        int64_t const its = ctx.P.num_iterations - hState[(size_t)i].remaining;
+        dv.stats.sum_iterations += its;
+        dv.stats.dp_cells += its * (int64_t)desc[(size_t)i].la * desc[(size_t)i].lb;
+    }
+    dv.stats.ms_setup += ev_ms(evS0, evS1);
+    for (int it = 0; it < itersRun; ++it)
+    {
+        dv.stats.ms_dp += ev_ms(dv.events[2 + 3 * (size_t)it], dv.events[2 + 3 * (size_t)it + 1]);
+        dv.stats.ms_bounds += ev_ms(dv.events[2 + 3 * (size_t)it + 1], dv.events[2 + 3 * (size_t)it + 2]);
+    }
+    dv.stats.n_pairs += n;
+    CK(cudaFreeAsync(dIdx, s));
+    CK(cudaFreeAsync(rC.ptr, s));
+    CK(cudaFreeAsync(rB.ptr, s));
+    CK(cudaFreeAsync(rA.ptr, s));
+    CK(cudaFreeAsync(dState, s));
+    CK(cudaFreeAsync(dDesc, s));
+}
+
+// Pairs per batch from the free device memory and a per-pair estimate (exact for the length dependent
+// part, heuristic for the edge/interaction arrays whose sizes are only known after set-up).
+size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin)
+{
+    size_t freeB = 0, totalB = 0;
+    cudaMemGetInfo(&freeB, &totalB);
+    double const budget = 0.45 * (double)freeB;
+    double used = 0;
+    size_t k = begin;
+    size_t const hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : 16384;
+    while (k < dv.pairs.size() && k - begin < hardCap)
+    {
+        OrientedPair const & op = dv.pairs[k];
+        double const C = (double)op.la * op.lb;
+        double const per = 4.0 * (C + 32.0 * (op.la + 34) * 4 + 64 * op.la) + 48.0 * C;
+        if (used + per > budget && k > begin) break;
+        used += per;
+        ++k;
+    }
+    return k;
+}
+
+void run_device(lara_ctx & ctx, Device & dv)
+{
+    try
+    {
+        CK(cudaSetDevice(dv.id));
+        std::memset(&dv.stats, 0, sizeof(dv.stats));
+        size_t begin = 0;
+        while (begin < dv.pairs.size())
+        {
+            size_t const end = batch_limit(ctx, dv, begin);
+            run_batch(ctx, dv, begin, end);
+            begin = end;
+        }
+        CK(cudaStreamSynchronize(dv.stream));
+    }
+    catch (std::exception const & e)
+    {
+        dv.err = e.what();
+        cudaGetLastError();
+    }
+}
+
+int set_err(lara_ctx * ctx, int code, std::string const & msg)
+{
+    if (ctx) ctx->err = msg; else g_createErr = msg;
+    return code;
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------
+extern "C" {
+
+int lara_gpu_version(void) { return LARA_ABI_VERSION; }
+
+int lara_gpu_visible_devices(void)
+{
+    int count = 0;
+    return cudaGetDeviceCount(&count) == cudaSuccess ? count : 0;
+}
+
+char const * lara_gpu_last_error(lara_ctx * ctx) { return ctx ? ctx->err.c_str() : g_createErr.c_str(); }
+
+int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, int const * device_ids)
+{
+    if (!out || !params) return set_err(nullptr, LARA_E_INVALID, "null argument");
+    *out = nullptr;
+    if (params->matching == 0)
+        return set_err(nullptr, LARA_E_UNSUPPORTED, "-m 0 (LEMON maximum weighted matching) is outside the GPU path");
+    if (params->matching > 8)
+        return set_err(nullptr, LARA_E_UNSUPPORTED, "greedy matching lookahead > 8 is not supported on the GPU path");
+    if (params->num_iterations < 1 || params->max_nondecreasing < 0)
+        return set_err(nullptr, LARA_E_INVALID, "invalid iteration parameters");
+    if (params->gap_open == params->gap_extend)
+        return set_err(nullptr, LARA_E_UNSUPPORTED,
+                       "gap open == gap extend switches the reference to linear gap costs (SeqAn dp_setup.h:322-325); "
+                       "not supported");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return set_err(nullptr, LARA_E_NO_DEVICE, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                                  " (lara_b200 has no CPU fallback)");
+    std::vector<int> ids;
+    if (n_devices <= 0 || !device_ids)
+    {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        ids.push_back(cur);
+    }
+    else
+        ids.assign(device_ids, device_ids + n_devices);
+    lara_ctx * ctx = new lara_ctx();
+    ctx->P = *params;
+    ctx->dp = make_dev_params(*params);
+    try
+    {
+        for (int id : ids)
+        {
+            if (id < 0 || id >= count) throw std::runtime_error("device id out of range");
+            cudaDeviceProp prop;
+            CK(cudaGetDeviceProperties(&prop, id));
+            if (prop.major < 10)
+                throw std::runtime_error(std::string("device ") + prop.name + " is not sm_100 (built for sm_100a only)");
+            ctx->devs.emplace_back();
+            Device & dv = ctx->devs.back();
+            dv.id = id;
+            CK(cudaSetDevice(id));
+            CK(cudaStreamCreateWithFlags(&dv.stream, cudaStreamNonBlocking));
+            CK(cudaMalloc((void **)&dv.negBuf, 64 * sizeof(int32_t)));
+            std::vector<int32_t> neg(64, kDpNeg);
+            CK(cudaMemcpy(dv.negBuf, neg.data(), 64 * sizeof(int32_t), cudaMemcpyHostToDevice));
+            CK(cudaMalloc((void **)&dv.dActive, sizeof(int32_t)));
+            CK(cudaMallocHost((void **)&dv.hActive, sizeof(int32_t)));
+            for (int k = 0; k < 2; ++k)
+            {
+                cudaEvent_t ev;
+                CK(cudaEventCreate(&ev));
+                dv.events.push_back(ev);
+            }
+            CK(post_configure_device());
+            // keep freed blocks in the stream-ordered pool between batches
+            cudaMemPool_t pool;
+            CK(cudaDeviceGetDefaultMemPool(&pool, id));
+            uint64_t thr = UINT64_MAX;
+            CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+        }
+    }
+    catch (std::exception const & ex)
+    {
+        g_createErr = ex.what();
+        lara_gpu_destroy(ctx);
+        return LARA_E_CUDA;
+    }
+    *out = ctx;
+    return LARA_OK;
+}
+
+void lara_gpu_destroy(lara_ctx * ctx)
+{
+    if (!ctx) return;
+    for (Device & dv : ctx->devs)
+    {
+        cudaSetDevice(dv.id);
+        if (dv.stream) cudaStreamSynchronize(dv.stream);
+        device_free_inputs(dv);
+        device_free_outputs(dv);
+        cudaFree(dv.negBuf);
+        cudaFree(dv.dActive);
+        if (dv.hActive) cudaFreeHost(dv.hActive);
+        for (cudaEvent_t ev : dv.events) cudaEventDestroy(ev);
+        if (dv.stream) cudaStreamDestroy(dv.stream);
+    }
+    delete ctx;
+}
+
+int lara_gpu_set_sequences(lara_ctx * ctx, int32_t n_seq, uint8_t const * seq_cat, int64_t const * seq_off,
+                           int32_t const * bp_partner, int32_t const * bp_weight, int64_t const * bp_off)
+{
+    if (!ctx) return LARA_E_INVALID;
+    if (n_seq < 0 || !seq_off || !bp_off) return set_err(ctx, LARA_E_INVALID, "null argument");
+    int64_t const total = seq_off[n_seq];
+    int64_t const nnz = bp_off[total];
+    for (int32_t i = 0; i < n_seq; ++i)
+    {
+        int64_t const L = seq_off[i + 1] - seq_off[i];
+        if (L < 1) return set_err(ctx, LARA_E_INVALID, "empty sequence");
+        if (L > 32 * kMaxR && false) return set_err(ctx, LARA_E_UNSUPPORTED, "sequence too long");
+        if (L > 32767) return set_err(ctx, LARA_E_UNSUPPORTED, "sequences longer than 32767 nt are not supported");
+        for (int64_t g = seq_off[i]; g < seq_off[i + 1]; ++g)
+        {
+            if (seq_cat[g] > 4) return set_err(ctx, LARA_E_INVALID, "sequence code outside 0..4");
+            for (int64_t x = bp_off[g]; x < bp_off[g + 1]; ++x)
+                if (bp_partner[x] < 0 || bp_partner[x] >= L) return set_err(ctx, LARA_E_INVALID, "base pair partner out of range");
+        }
+    }
+    ctx->nSeq = n_seq;
+    ctx->seqOff.assign(seq_off, seq_off + n_seq + 1);
+    ctx->bpOff.assign(bp_off, bp_off + total + 1);
+    ctx->nbp.assign((size_t)n_seq, 0);
+    for (int32_t i = 0; i < n_seq; ++i)
+        ctx->nbp[(size_t)i] = (int32_t)((bp_off[seq_off[i + 1]] - bp_off[seq_off[i]] + 1) / 2);
+    ctx->prepared = false;
+    try
+    {
+        for (Device & dv : ctx->devs)
+        {
+            CK(cudaSetDevice(dv.id));
+            device_free_inputs(dv);
+            cudaEvent_t e0 = dv.events[0], e1 = dv.events[1];
+            CK(cudaEventRecord(e0, dv.stream));
+            CK(cudaMalloc(&dv.dSeq, (size_t)std::max<int64_t>(total, 1)));
+            CK(cudaMalloc(&dv.dSeqOff, sizeof(int64_t) * (size_t)(n_seq + 1)));
+            CK(cudaMalloc(&dv.dBpOff, sizeof(int64_t) * (size_t)(total + 1)));
+            CK(cudaMalloc(&dv.dBpPartner, sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1)));
+            CK(cudaMalloc(&dv.dBpWeight, sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1)));
+            CK(cudaMemcpyAsync(dv.dSeq, seq_cat, (size_t)total, cudaMemcpyHostToDevice, dv.stream));
+            CK(cudaMemcpyAsync(dv.dSeqOff, seq_off, sizeof(int64_t) * (size_t)(n_seq + 1), cudaMemcpyHostToDevice, dv.stream));
+            CK(cudaMemcpyAsync(dv.dBpOff, bp_off, sizeof(int64_t) * (size_t)(total + 1), cudaMemcpyHostToDevice, dv.stream));
+            if (nnz)
+            {
+                CK(cudaMemcpyAsync(dv.dBpPartner, bp_partner, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, dv.stream));
+                CK(cudaMemcpyAsync(dv.dBpWeight, bp_weight, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, dv.stream));
+            }
+            CK(cudaEventRecord(e1, dv.stream));
+            CK(cudaStreamSynchronize(dv.stream));
+            dv.in.seqCat = (uint8_t const *)dv.dSeq; dv.in.seqOff = (int64_t const *)dv.dSeqOff;
+            dv.in.bpOff = (int64_t const *)dv.dBpOff; dv.in.bpPartner = (int32_t const *)dv.dBpPartner;
+            dv.in.bpWeight = (int32_t const *)dv.dBpWeight;
+            ctx->stats.ms_h2d = ev_ms(e0, e1);
+        }
+        ctx->stats.h2d_bytes = total + 8 * (n_seq + 1) + 8 * (total + 1) + 8 * nnz;
+    }
+    catch (std::exception const & ex)
+    {
+        return set_err(ctx, LARA_E_CUDA, ex.what());
+    }
+    return LARA_OK;
+}
+
+int lara_gpu_prepare_pairs(lara_ctx * ctx, int64_t n_pairs, int32_t const * idx_a, int32_t const * idx_b)
+{
+    if (!ctx) return LARA_E_INVALID;
+    if (n_pairs < 0 || (n_pairs > 0 && (!idx_a || !idx_b))) return set_err(ctx, LARA_E_INVALID, "null argument");
+    if (ctx->seqOff.empty()) return set_err(ctx, LARA_E_INVALID, "lara_gpu_set_sequences must be called first");
+    std::vector<OrientedPair> all((size_t)n_pairs);
+    for (int64_t p = 0; p < n_pairs; ++p)
+    {
+        int32_t const i = std::min(idx_a[p], idx_b[p]), j = std::max(idx_a[p], idx_b[p]);
+        if (i < 0 || j >= ctx->nSeq || i == j) return set_err(ctx, LARA_E_INVALID, "pair index out of range");
+        int32_t const li = (int32_t)(ctx->seqOff[i + 1] - ctx->seqOff[i]), lj = (int32_t)(ctx->seqOff[j + 1] - ctx->seqOff[j]);
+        OrientedPair & op = all[(size_t)p];
+        if (li >= lj) { op.first = i; op.second = j; op.la = li; op.lb = lj; }       // solver :117-120
+        else { op.first = j; op.second = i; op.la = lj; op.lb = li; }
+        op.request = p;
+        if ((op.lb + 31) / 32 > kMaxR)
+            return set_err(ctx, LARA_E_UNSUPPORTED, "shorter sequence of a pair exceeds " + std::to_string(32 * kMaxR) +
+                                                     " nt (single-pass DP limit of this build)");
+    }
+    // longest first, like the reference's queue (CompareSeqLength, src/io.hpp:352-365)
+    std::stable_sort(all.begin(), all.end(), [](OrientedPair const & x, OrientedPair const & y) {
+        return x.la != y.la ? x.la > y.la : x.lb > y.lb;
+    });
+    try
+    {
+        size_t const nd = ctx->devs.size();
+        for (size_t k = 0; k < nd; ++k)
+        {
+            Device & dv = ctx->devs[k];
+            CK(cudaSetDevice(dv.id));
+            device_free_outputs(dv);
+            dv.pairs.clear();
+            for (size_t q = k; q < all.size(); q += nd) dv.pairs.push_back(all[q]);   // interleaved shares
+            dv.outOff.assign(dv.pairs.size() + 1, 0);
+            for (size_t q = 0; q < dv.pairs.size(); ++q) dv.outOff[q + 1] = dv.outOff[q] + 3ll * dv.pairs[q].lb;
+            dv.outLinesTotal = dv.outOff.back();
+            size_t const np = std::max<size_t>(dv.pairs.size(), 1);
+            CK(cudaMalloc((void **)&dv.dOutHdr, sizeof(PairOutHdr) * np));
+            CK(cudaMalloc((void **)&dv.dOutLines, sizeof(int32_t) * (size_t)std::max<int64_t>(dv.outLinesTotal, 1)));
+            CK(cudaMalloc((void **)&dv.dOutOff, sizeof(int64_t) * (np + 1)));
+            CK(cudaMemcpy(dv.dOutOff, dv.outOff.data(), sizeof(int64_t) * dv.outOff.size(), cudaMemcpyHostToDevice));
+        }
+    }
+    catch (std::exception const & ex)
+    {
+        return set_err(ctx, LARA_E_CUDA, ex.what());
+    }
+    ctx->nPrepared = n_pairs;
+    ctx->prepared = true;
+    ctx->ran = false;
+    return LARA_OK;
+}
+
+int lara_gpu_run_prepared(lara_ctx * ctx)
+{
+    if (!ctx) return LARA_E_INVALID;
+    if (!ctx->prepared) return set_err(ctx, LARA_E_INVALID, "no prepared pairs");
+    auto const t0 = std::chrono::steady_clock::now();
+    if (ctx->devs.size() == 1)
+        run_device(*ctx, ctx->devs[0]);
+    else
+    {
+        std::vector<std::thread> th;
+        for (Device & dv : ctx->devs) th.emplace_back([ctx, &dv]() { run_device(*ctx, dv); });
+        for (std::thread & t : th) t.join();
+    }
+    double const ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    lara_stats agg{};
+    agg.ms_h2d = ctx->stats.ms_h2d; agg.h2d_bytes = ctx->stats.h2d_bytes;
+    for (Device & dv : ctx->devs)
+    {
+        if (!dv.err.empty()) { std::string e = dv.err; dv.err.clear(); return set_err(ctx, LARA_E_CUDA, e); }
+        agg.ms_setup = std::max(agg.ms_setup, dv.stats.ms_setup);
+        agg.ms_dp = std::max(agg.ms_dp, dv.stats.ms_dp);
+        agg.ms_bounds = std::max(agg.ms_bounds, dv.stats.ms_bounds);
+        agg.dp_cells += dv.stats.dp_cells; agg.dp_launches += dv.stats.dp_launches;
+        agg.kernel_launches += dv.stats.kernel_launches; agg.filter_cells += dv.stats.filter_cells;
+        agg.n_pairs += dv.stats.n_pairs; agg.sum_iterations += dv.stats.sum_iterations;
+        agg.n_active_edges += dv.stats.n_active_edges; agg.n_interactions += dv.stats.n_interactions;
+    }
+    agg.ms_total = ms;
+    ctx->stats = agg;
+    ctx->ran = true;
+    return LARA_OK;
+}
+
+int lara_gpu_fetch_prepared(lara_ctx * ctx, lara_results * out)
+{
+    if (!ctx || !out) return LARA_E_INVALID;
+    if (!ctx->ran) return set_err(ctx, LARA_E_INVALID, "lara_gpu_run_prepared has not run");
+    ResultOwner * own = new ResultOwner();
+    own->pairs.resize((size_t)ctx->nPrepared);
+    try
+    {
+        struct Got { std::vector<PairOutHdr> hdr; std::vector<int32_t> lines; };
+        std::vector<Got> got(ctx->devs.size());
+        int64_t d2h = 0;
+        double msD2h = 0;
+        for (size_t k = 0; k < ctx->devs.size(); ++k)
+        {
+            Device & dv = ctx->devs[k];
+            CK(cudaSetDevice(dv.id));
+            got[k].hdr.resize(dv.pairs.size());
+            got[k].lines.resize((size_t)dv.outLinesTotal);
+            CK(cudaEventRecord(dv.events[0], dv.stream));
+            if (!dv.pairs.empty())
+            {
+                CK(cudaMemcpyAsync(got[k].hdr.data(), dv.dOutHdr, sizeof(PairOutHdr) * dv.pairs.size(), cudaMemcpyDeviceToHost, dv.stream));
+                CK(cudaMemcpyAsync(got[k].lines.data(), dv.dOutLines, sizeof(int32_t) * (size_t)dv.outLinesTotal, cudaMemcpyDeviceToHost, dv.stream));
+            }
+            CK(cudaEventRecord(dv.events[1], dv.stream));
+            CK(cudaStreamSynchronize(dv.stream));
+            msD2h = std::max(msD2h, ev_ms(dv.events[0], dv.events[1]));
+            d2h += (int64_t)(sizeof(PairOutHdr) * dv.pairs.size() + sizeof(int32_t) * (size_t)dv.outLinesTotal);
+        }
+        ctx->stats.ms_d2h = msD2h;
+        ctx->stats.d2h_bytes = d2h;
+        // request order
+        std::vector<std::pair<size_t, size_t>> where((size_t)ctx->nPrepared);
+        for (size_t k = 0; k < ctx->devs.size(); ++k)
+            for (size_t q = 0; q < ctx->devs[k].pairs.size(); ++q)
+                where[(size_t)ctx->devs[k].pairs[q].request] = {k, q};
+        for (int64_t p = 0; p < ctx->nPrepared; ++p)
+        {
+            size_t const k = where[(size_t)p].first, q = where[(size_t)p].second;
+            Device & dv = ctx->devs[k];
+            OrientedPair const & op = dv.pairs[q];
+            PairOutHdr const & h = got[k].hdr[q];
+            lara_pair_result & r = own->pairs[(size_t)p];
+            r.idx_low = std::min(op.first, op.second);
+            r.idx_high = std::max(op.first, op.second);
+            r.best_lower = h.bestLower; r.best_upper = h.bestUpper; r.iterations = h.iterations; r.n_lines = h.nLines;
+            r.lines_off = (int64_t)own->posLow.size();
+            int32_t const * base = got[k].lines.data() + dv.outOff[q];
+            for (int32_t x = 0; x < h.nLines; ++x)
+            {
+                own->posLow.push_back(base[x]);
+                own->posHigh.push_back(base[op.lb + x]);
+                own->weight.push_back((uint32_t)base[2 * op.lb + x]);
+            }
+        }
+    }
+    catch (std::exception const & ex)
+    {
+        delete own;
+        return set_err(ctx, LARA_E_CUDA, ex.what());
+    }
+    out->n_pairs = ctx->nPrepared;
+    out->pairs = own->pairs.data();
+    out->n_lines_total = (int64_t)own->posLow.size();
+    out->line_pos_low = own->posLow.data();
+    out->line_pos_high = own->posHigh.data();
+    out->line_weight = own->weight.data();
+    out->owner_ = own;
+    return LARA_OK;
+}
+
+int lara_gpu_solve_pairs(lara_ctx * ctx, int64_t n_pairs, int32_t const * idx_a, int32_t const * idx_b, lara_results * out)
+{
+    int rc = lara_gpu_prepare_pairs(ctx, n_pairs, idx_a, idx_b);
+    if (rc != LARA_OK) return rc;
+    rc = lara_gpu_run_prepared(ctx);
+    if (rc != LARA_OK) return rc;
+    return lara_gpu_fetch_prepared(ctx, out);
+}
+
+int lara_gpu_solve_all_pairs(lara_ctx * ctx, lara_results * out)
+{
+    if (!ctx) return LARA_E_INVALID;
+    std::vector<int32_t> a, b;
+    for (int32_t i = 0; i + 1 < ctx->nSeq; ++i)
+        for (int32_t j = i + 1; j < ctx->nSeq; ++j) { a.push_back(i); b.push_back(j); }
+    return lara_gpu_solve_pairs(ctx, (int64_t)a.size(), a.data(), b.data(), out);
+}
+
+void lara_gpu_free_results(lara_results * out)
+{
+    if (out && out->owner_)
+    {
+        delete static_cast<ResultOwner *>(out->owner_);
+        std::memset(out, 0, sizeof(*out));
+    }
+}
+
+int lara_gpu_get_stats(lara_ctx * ctx, lara_stats * stats)
+{
+    if (!ctx || !stats) return LARA_E_INVALID;
+    *stats = ctx->stats;
+    return LARA_OK;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// unit-level entry points (parity tests of single kernels)
+// ---------------------------------------------------------------------------------------------------
+extern "C" {
+
+int lara_gpu_gotoh_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32_t lenB, int32_t const * pssm,
+                         int32_t gap_open, int32_t gap_extend, int32_t * score, int32_t * n_lines, int32_t * lines_a,
+                         int32_t * lines_b, int32_t * gap_score)
+{
+    if (!ctx || !pssm || n_problems < 1 || lenA < 1 || lenB < 1) return set_err(ctx, LARA_E_INVALID, "bad argument");
+    if ((lenB + 31) / 32 > kMaxR) return set_err(ctx, LARA_E_UNSUPPORTED, "lenB exceeds the single-pass DP limit");
+    Device & dv = ctx->devs[0];
+    cudaStream_t const s = dv.stream;
+    int const n = n_problems;
+    try
+    {
+        CK(cudaSetDevice(dv.id));
+        std::vector<PairDesc> desc((size_t)n);
+        Region rg;
+        for (int pass = 0; pass < 2; ++pass)
+        {
+            rg.used = 0;
+            for (int i = 0; i < n; ++i)
+            {
+                PairDesc & d = desc[(size_t)i];
+                std::memset(&d, 0, sizeof(d));
+                d.la = lenA; d.lb = lenB; d.R = (lenB + 31) / 32; d.W = d.R <= 8 ? 1 : (d.R <= 16 ? 2 : 4);
+                d.nSteps = (lenA + 31 + 3) & ~3; d.bitWords = (lenB + 31) / 32;
+                d.nVals = 32 * lenA * d.R;
+                d.offFlags = rg.take(32ll * ((d.nSteps + 31) / 32));
+                d.offLanePtr = rg.take(32);
+                d.offVals = rg.take(d.nVals);
+                d.offTrace = rg.take(32ll * d.nSteps * d.W);
+                d.offLines = rg.take(lenB);
+            }
+            if (pass == 0) CK(cudaMalloc((void **)&rg.ptr, (size_t)rg.used * 4));
+        }
+        int32_t * arena = rg.ptr;
+        PairDesc * dDesc; PairState * dState; int32_t * dPssm;
+        size_t const nP = (size_t)n * lenA * lenB;
+        CK(cudaMalloc((void **)&dDesc, sizeof(PairDesc) * (size_t)n));
+        CK(cudaMalloc((void **)&dState, sizeof(PairState) * (size_t)n));
+        CK(cudaMalloc((void **)&dPssm, sizeof(int32_t) * nP));
+        CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
+        CK(cudaMemsetAsync(dState, 0, sizeof(PairState) * (size_t)n, s));
+        CK(cudaMemcpyAsync(dPssm, pssm, sizeof(int32_t) * nP, cudaMemcpyHostToDevice, s));
+        CK(launch_dense_to_stream(n, dDesc, arena, dPssm, s));
+        CK(launch_gotoh_fill(desc[0].R, n, nullptr, dDesc, dState, arena, dv.negBuf, gap_open, gap_extend, s));
+        CK(launch_traceback_only(n, dDesc, dState, arena, gap_open, gap_extend, lenA, lenB, s));
+        std::vector<PairState> hs((size_t)n);
+        CK(cudaMemcpyAsync(hs.data(), dState, sizeof(PairState) * (size_t)n, cudaMemcpyDeviceToHost, s));
+        std::vector<int32_t> lines((size_t)n * lenB);
+        for (int i = 0; i < n; ++i)
+            CK(cudaMemcpyAsync(lines.data() + (size_t)i * lenB, arena + desc[(size_t)i].offLines, sizeof(int32_t) * (size_t)lenB,
+                               cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        for (int i = 0; i < n; ++i)
+        {
+            if (score) score[i] = hs[(size_t)i].currentUpper;
+            if (n_lines) n_lines[i] = hs[(size_t)i].nLines;
+            if (gap_score) gap_score[i] = hs[(size_t)i].gapScore;
+            for (int k = 0; k < hs[(size_t)i].nLines; ++k)
+            {
+                uint32_t const v = (uint32_t)lines[(size_t)i * lenB + k];
+                if (lines_a) lines_a[(size_t)i * lenB + k] = (int32_t)(v >> 16);
+                if (lines_b) lines_b[(size_t)i * lenB + k] = (int32_t)(v & 0xffffu);
+            }
+        }
+        cudaFree(dPssm); cudaFree(dState); cudaFree(dDesc); cudaFree(arena);
+    }
+    catch (std::exception const & ex)
+    {
+        return set_err(ctx, LARA_E_CUDA, ex.what());
+    }
+    return LARA_OK;
+}
+
+int lara_gpu_edge_filter(lara_ctx * ctx, uint8_t const * seqA, int32_t lenA, uint8_t const * seqB, int32_t lenB,
+                         uint8_t * active, int32_t * opt_score)
+{
+    if (!ctx || !seqA || !seqB || lenA < 1 || lenB < 1 || !active) return set_err(ctx, LARA_E_INVALID, "bad argument");
+    Device & dv = ctx->devs[0];
+    cudaStream_t const s = dv.stream;
+    try
+    {
+        CK(cudaSetDevice(dv.id));
+        // a private two-sequence input set
+        std::vector<uint8_t> cat(seqA, seqA + lenA);
+        cat.insert(cat.end(), seqB, seqB + lenB);
+        int64_t off[3] = {0, lenA, (int64_t)lenA + lenB};
+        uint8_t * dCat; int64_t * dOff;
+        CK(cudaMalloc((void **)&dCat, cat.size()));
+        CK(cudaMalloc((void **)&dOff, sizeof(off)));
+        CK(cudaMemcpyAsync(dCat, cat.data(), cat.size(), cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(dOff, off, sizeof(off), cudaMemcpyHostToDevice, s));
+        DevInputs in{};
+        in.seqCat = dCat; in.seqOff = dOff;
+        PairDesc d{};
+        d.la = lenA; d.lb = lenB; d.seqFirst = 0; d.seqSecond = 1; d.bitWords = (lenB + 31) / 32;
+        Region rg;
+        d.offBits = rg.take((int64_t)lenA * d.bitWords);
+        d.offScratch = rg.take((int64_t)lenA * lenB + 6ll * (lenA + 1));
+        CK(cudaMalloc((void **)&rg.ptr, (size_t)rg.used * 4));
+        PairDesc * dDesc; PairState * dState;
+        CK(cudaMalloc((void **)&dDesc, sizeof(PairDesc)));
+        CK(cudaMalloc((void **)&dState, sizeof(PairState)));
+        CK(cudaMemcpyAsync(dDesc, &d, sizeof(d), cudaMemcpyHostToDevice, s));
+        CK(cudaMemsetAsync(dState, 0, sizeof(PairState), s));
+        CK(launch_edge_filter(1, dDesc, dState, rg.ptr, in, ctx->dp, s));
+        std::vector<uint32_t> bits((size_t)lenA * d.bitWords);
+        PairState hs;
+        CK(cudaMemcpyAsync(bits.data(), rg.ptr + d.offBits, bits.size() * 4, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(&hs, dState, sizeof(hs), cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        for (int a = 0; a < lenA; ++a)
+            for (int b = 0; b < lenB; ++b)
+                active[(size_t)a * lenB + b] = (uint8_t)((bits[(size_t)a * d.bitWords + (b >> 5)] >> (b & 31)) & 1u);
+        if (opt_score) *opt_score = hs.optScore;
+        cudaFree(dState); cudaFree(dDesc); cudaFree(rg.ptr); cudaFree(dOff); cudaFree(dCat);
+    }
+    catch (std::exception const & ex)
+    {
+        return set_err(ctx, LARA_E_CUDA, ex.what());
+    }
+    return LARA_OK;
+}
+
+int lara_gpu_int_issue_rate(lara_ctx * ctx, int kind, double * gops)
+{
+    if (!ctx || !gops) return LARA_E_INVALID;
+    Device & dv = ctx->devs[0];
+    try
+    {
+        CK(cudaSetDevice(dv.id));
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, dv.id));
+        int32_t * dOut;
+        CK(cudaMalloc((void **)&dOut, 4));
+        int const blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+        CK(launch_int_issue(kind, blocks, threads, 64, dOut, dv.stream));      // warm-up
+        CK(cudaEventRecord(dv.events[0], dv.stream));
+        CK(launch_int_issue(kind, blocks, threads, iters, dOut, dv.stream));
+        CK(cudaEventRecord(dv.events[1], dv.stream));
+        CK(cudaStreamSynchronize(dv.stream));
+        double const ms = ev_ms(dv.events[0], dv.events[1]);
+        double const perOp = kind == 0 ? 1.0 : (kind == 1 ? 2.0 : 5.0);
+        double const ops = (double)blocks * threads * (double)iters * 32.0 * perOp;
+        *gops = ops / (ms * 1e-3) / 1e9;
+        cudaFree(dOut);
+    }
+    catch (std::exception const & ex)
+    {
+        return set_err(ctx, LARA_E_CUDA, ex.what());
+    }
+    return LARA_OK;
+}
+
+} // extern "C"

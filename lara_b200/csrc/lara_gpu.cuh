@@ -1,0 +1,157 @@
+// lara_gpu.cuh -- shared device-side definitions of the B200 LaRA hot path.
+//
+// Execution model: a batch of sequence pairs advances through the subgradient
+// iterations in lock step; every iteration is two kernel launches over the batch,
+//   1. gotoh_fill_kernel<R>   one warp per pair, the affine-gap DP over the full lenA x lenB matrix
+//   2. iterate_post_kernel    one warp per pair: traceback, valid_solution + greedy matching,
+//                             bounds / step size / multiplier update, pssm refresh
+// and the per-pair Lagrange problem lives in HBM in the flat layout described below.
+#ifndef LARA_GPU_CUH_
+#define LARA_GPU_CUH_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/lara_b200.h"
+
+namespace lara
+{
+
+// SeqAn:align/dp_cell.h:143-146  (lowest()/2) -- "minus infinity" of the DP borders.
+constexpr int32_t kDpNeg = INT32_MIN / 2;
+// src/score.hpp:92 -- pssm value of inactive cells.  Only "never wins against a gap path" matters.
+constexpr int32_t kPssmInit = -1431655764;
+// src/data_types.hpp:77
+constexpr int32_t kInf = LARA_INFINITY;
+
+constexpr int kWarp = 32;
+// Largest rows-per-lane the single-pass DP kernel is instantiated for: lenB <= 32 * kMaxR.
+constexpr int kMaxR = 20;
+
+// Trace nibble of one DP cell: the four decisions of SeqAn's _computeScore, each
+// bit set when the RIGHT operand of _maxScore won (the left one wins ties).  A lane pushes the nibbles of
+// its R cells MSB-first into ceil(R/8) words per step: cell j sits in word j/8 at bit 4*(n-1-(j%8)) where n
+// is the number of cells in that word.
+enum : uint32_t
+{
+    kTrGap   = 1u,  // S = best gap score (else: diagonal)                 -> !DIAGONAL
+    kTrFromH = 2u,  // best gap matrix is H (else: V)                      -> MAX_FROM_HORIZONTAL_MATRIX
+    kTrVOpen = 4u,  // V opened from S (else: extended)                    -> VERTICAL_OPEN
+    kTrHOpen = 8u   // H opened from S (else: extended)                    -> HORIZONTAL_OPEN
+};
+
+// Static description of one pair in the batch (written by the host after the set-up counts are known).
+// All off* are offsets in 4-byte units into the batch arena.
+struct PairDesc
+{
+    int32_t la, lb;             // lengths; A = first = longer sequence = DP columns (H), B = rows (V)
+    int32_t seqFirst, seqSecond;// sequence indices (first is the longer one, src/subgradient_solver.hpp:117-120)
+    int32_t R;                  // rows per lane of the DP: ceil(lb / 32)
+    int32_t W;                  // trace words per lane and step: ceil(R / 8)
+    int32_t nSteps;             // la + 31 rounded up to a multiple of 4
+    int32_t E;                  // active alignment edges
+    int32_t D;                  // interactions == dual variables (Lagrange::dimension)
+    int32_t nVals;              // entries of the strip-dense pssm stream
+    int32_t bitWords;           // words per row of the active bitmap: ceil(lb / 32)
+    int32_t kCap;               // upper bound of matching candidates per iteration
+    int64_t offBits;            // active bitmap   [la][bitWords]
+    int64_t offRowStart;        // first compact edge id of bitmap row a  [la + 1]
+    int64_t offFlags;           // per lane step flags: bit (t & 31) of word [lane][t >> 5], nFlagWords words per lane
+    int64_t offLanePtr;         // [32] start of each lane's value stream (relative to offVals)
+    int64_t offVals;            // strip-dense pssm stream [nVals]
+    int64_t offTrace;           // trace words [32 lanes][nSteps][W]
+    int64_t offCell;            // per edge: (a << 16) | b          [E]
+    int64_t offSeqScore;        // per edge: getSeqScore            [E]
+    int64_t offPv;              // per edge: top of its priority queue == pssm value [E]
+    int64_t offPerm;            // per edge: position in the value stream [E]
+    int64_t offIoff;            // per edge: CSR row start in the interaction arrays [E + 1]
+    int64_t offPart;            // per interaction: partner edge id  [D]
+    int64_t offPpos;            // per interaction: partner (a << 16) | b [D]
+    int64_t offSc;              // per interaction: structure score  [D]
+    int64_t offDual;            // per interaction: Lagrange multiplier [D]
+    int64_t offRev;             // per interaction: index of the reverse interaction [D]
+    int64_t offList;            // subgradient index list (sign in bit 31) [D]
+    int64_t offLines;           // current lines  (a << 16) | b  [lb]
+    int64_t offBest;            // best lines     (a << 16) | b | matched << 31  [lb]
+    int64_t offCand;            // global candidate buffer for the matching sort, 2 words each [2 * kCap] (8-byte aligned)
+    int64_t offScratch;         // set-up scratch: forward prefix scores [la * lb]
+};
+
+// Mutable per-pair solver state (BoundInfo + SubgradientSolver fields, src/subgradient_solver.hpp:64-108).
+struct PairState
+{
+    int32_t bestLower, bestUpper, currentLower, currentUpper;
+    uint32_t nondecreasing;
+    float stepFactorF;          // scalar build: float stepSizeFactor
+    int32_t stepFactorI;        // SIMD build: int32 step factor (src/subgradient_solver_simd.hpp:153)
+    int32_t remaining;          // remainingIterations
+    int32_t done;               // 1 once the pair has finished (result written)
+    int32_t sEnd, vEnd, hEnd;   // S, V, H of the last DP cell (end-cell trace correction)
+    int32_t bestScore;          // Lagrange::bestStructuralAlignmentScore
+    int32_t nBest;              // number of best lines
+    int32_t nLines, gapScore;   // last alignment
+    int32_t nList;              // subgradientIndices.size()
+    int32_t optScore;           // edge filter optimum (forward == backward)
+    float   scale;              // sequenceScaleFactor (src/lagrange.hpp:252)
+    int32_t error;              // non-zero: internal invariant violated
+    int32_t pad_[3];
+};
+
+// Solver parameters in device constant form.
+struct DevParams
+{
+    int32_t numIterations, maxNondecreasing, lookahead, stepMode;
+    float stepSizeFactor, balance, sequenceScale;
+    int32_t subopt;             // int32(suboptimalDiff * 8192)
+    int32_t go, ge;
+    int32_t tab[25];
+    uint32_t libMin, libMax;
+    int32_t libLinear;
+};
+
+// Read-only inputs shared by all pairs of a context.
+struct DevInputs
+{
+    uint8_t const * seqCat;
+    int64_t const * seqOff;
+    int32_t const * bpPartner;
+    int32_t const * bpWeight;
+    int64_t const * bpOff;
+};
+
+// Output slot of one pair (copied back to the host as is).
+struct PairOutHdr
+{
+    int32_t bestLower, bestUpper, iterations, nLines;
+};
+
+// ---- launchers (one translation unit each) -------------------------------------------------
+// DP fill over the pairs listed in pairIdx[0..n) that all have the same R.
+cudaError_t launch_gotoh_fill(int R, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
+                              int32_t * arena, int32_t const * negBuf, int32_t go, int32_t ge, cudaStream_t stream);
+// traceback + valid_solution + matching + bounds + update for all n pairs of the batch
+cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
+                                DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
+                                int32_t * activeCount, int maxLa, int maxLb, int smemCand, cudaStream_t stream);
+// traceback only (unit entry point lara_gpu_gotoh_batch)
+cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * state, int32_t * arena,
+                                  int32_t go, int32_t ge, int maxLa, int maxLb, cudaStream_t stream);
+// per-device one-time configuration of the post kernels (shared memory opt-in)
+cudaError_t post_configure_device();
+// set-up stage 1: edge filter -> bitmap, optimum score, E
+cudaError_t launch_edge_filter(int n, PairDesc * desc, PairState * state, int32_t * arena, DevInputs in,
+                               DevParams const & P, cudaStream_t stream);
+// set-up stage 2: rowStart, cell ids, sequence scores, interaction counts -> D, stream geometry -> nVals
+cudaError_t launch_setup_count(int n, PairDesc * desc, PairState * state, int32_t * arena, DevInputs in,
+                               DevParams const & P, cudaStream_t stream);
+// set-up stage 3: interactions, reverse indices, initial pssm, value stream
+cudaError_t launch_setup_fill(int n, PairDesc * desc, PairState * state, int32_t * arena, DevInputs in,
+                              DevParams const & P, cudaStream_t stream);
+// dense pssm -> strip-dense stream with all cells active (unit entry point)
+cudaError_t launch_dense_to_stream(int n, PairDesc const * desc, int32_t * arena, int32_t const * pssm,
+                                   cudaStream_t stream);
+// integer issue-rate microbenchmark
+cudaError_t launch_int_issue(int kind, int blocks, int threads, int iters, int32_t * out, cudaStream_t stream);
+
+} // namespace lara
+#endif

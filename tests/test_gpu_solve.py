@@ -1,0 +1,75 @@
+"""GPU parity tests of the whole hot path through the C ABI (-m gpu): lara_gpu_solve_* against the CPU
+restatement on the same seeded inputs.  Bit-exact: lines, library weights, bounds and iteration counts."""
+import numpy as np
+import pytest
+
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _solve_both(files, n_threads=8, pairs=None, **kw):
+    import lara_b200 as lb
+    from oracle import binding as ob
+    store = util.load_store(files)
+    p = lb.Parameters()
+    p.set(**kw)
+    flat = store.flat()
+    ia, ib = ob.all_pairs(len(store)) if pairs is None else pairs
+    ctx = lb.Context(p)
+    ctx.set_sequences(flat)
+    rg = ctx.solve_pairs(ia, ib)
+    got = lb.results_to_list(rg)
+    st = ctx.stats()
+    ctx.free(rg)
+    ro, _ = ob.solve_pairs(p, flat, ia, ib, n_threads=n_threads)
+    want = lb.results_to_list(ro)
+    ob.free_results(ro)
+    ctx.close()
+    return got, want, st
+
+
+@pytest.mark.parametrize("kw", [
+    dict(num_iterations=60, max_nondecreasing=8),
+    dict(num_iterations=40, max_nondecreasing=5, step_mode=1),
+    dict(num_iterations=40, matching=3),
+    dict(num_iterations=40, matching=1, balance=0.7),
+    dict(num_iterations=40, sequence_scale=1.5, step_size_factor=1.7),
+    dict(num_iterations=40, lib_score_linear=1, lib_score_min=100, lib_score_max=900),
+])
+def test_solve_ebpseq_small(built, kw):
+    files = util.make_input(seed=31, n=7, length=60, lenmax=90)
+    got, want, st = _solve_both(files, **kw)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+    assert st.dp_launches > 0 and st.kernel_launches > st.dp_launches
+
+
+def test_solve_dbn_early_termination(built):
+    files = util.make_input(seed=32, n=8, length=70, lenmax=110, fmt="dbn", related=False)
+    got, want, _ = _solve_both(files)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+    assert min(r.iterations for r in got) < 500
+
+
+def test_solve_unrelated_lengths(built):
+    files = util.make_input(seed=33, n=8, length=35, lenmax=160, related=False)
+    got, want, _ = _solve_both(files, num_iterations=50, max_nondecreasing=6)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+
+
+def test_solve_dotplots(built):
+    files = util.make_input(seed=34, n=4, length=100, lenmax=120, fmt="dp")
+    got, want, _ = _solve_both(files, num_iterations=60)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+
+
+def test_solve_default_500_iterations(built):
+    files = util.make_input(seed=35, n=6, length=120)
+    got, want, _ = _solve_both(files)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+
+
+def test_solve_300nt(built):
+    files = util.make_input(seed=36, n=5, length=300)
+    got, want, _ = _solve_both(files, num_iterations=80, max_nondecreasing=10)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
