@@ -1,0 +1,401 @@
+#!/usr/bin/env python3
+"""Benchmark of the hot path: LaRA 2's all-pairs Lagrangian subgradient loop on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (N=1: plain python; N>1: under torchrun, one rank per GPU)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+One "step" = one pass of the hot path (lara::solve, src/subgradient_solver.hpp:110) over the whole workload:
+BASELINE.json configs[2] (C3): 500 synthetic RNAs x 300 nt, `.ebpseq` base pair weights, all 124,750 pairs,
+reference default options (500 iterations).  With N ranks the fixed pair set is dealt round-robin from the
+length-sorted list to the ranks (no collective on the data path; strong scaling).
+
+Prints ONE JSON line (rank 0).  Keys beyond the base contract:
+  value        pairs/s with the inputs resident in HBM when the timed region starts (device CUDA-event span)
+  e2e          the same metric through the C ABI with HOST buffers (lara_gpu_set_sequences + lara_gpu_solve_pairs
+               + results copied to host memory), wall clock, every step
+  gcups        DP cell updates/s (sum over pairs and iterations of lenA*lenB) / 1e9
+  roofline     DP fill kernel: achieved = 9 int32 ops per cell * cells / summed CUDA-event
+               duration of the DP launches; peak = int32 lane-op issue rate measured on this GPU by the library's
+               microbenchmark; plus the kernel's algorithmic HBM traffic against MEASURED_PEAKS.json
+  cpu_baseline the UNMODIFIED reference binary (oracle/_ref/lara_scalar, built from /root/reference by
+               oracle/build_ref.sh) on this box's host cores, on a bounded sample of the same workload
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+OPS_PER_CELL = 9.0          # 5 IADD + 4 tie-aware maxima
+SAMPLE_SEQS_CPU = 24        # cpu_baseline / reference arm: first 24 of the workload's sequences (276 pairs)
+
+WORKLOADS = {
+    "c1": dict(seed=1, n=10, length=120, fmt="dbn"),
+    "c2": dict(seed=2, n=100, length=150, fmt="ebpseq"),
+    "c3": dict(seed=3, n=500, length=300, fmt="ebpseq"),
+}
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def make_workload(name, nseq=0):
+    import gen_inputs
+    w = dict(WORKLOADS[name])
+    d = tempfile.mkdtemp(prefix="lara_bench_%s_" % name)
+    files = gen_inputs.generate(d, w["seed"], w["n"], w["length"], w["fmt"])
+    if nseq and nseq < w["n"]:
+        files = [subset_file(files[0], nseq, os.path.join(d, "subset." + w["fmt"]))]
+        w["n"] = nseq
+    return w, files
+
+
+def subset_file(path, m, out):
+    """First m records of a generated .ebpseq / .dbn file, byte-identical per record."""
+    lines = open(path).read().split("\n")
+    res = []
+    if path.endswith(".dbn"):
+        res = lines[:3 * m]
+    else:
+        rec = 0
+        for ln in lines:
+            if ln.startswith("## S"):
+                k = int(ln[4:ln.index(":")])
+                if k <= m:
+                    res.append(ln)
+            elif ln.startswith("## "):
+                res.append(ln)
+            elif ln.startswith("# S"):
+                rec = int(ln[3:])
+                if rec <= m:
+                    res.append(ln)
+            elif rec <= m:
+                res.append(ln)
+    with open(out, "w") as f:
+        f.write("\n".join(res).rstrip("\n") + "\n")
+    return out
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append([x.strip() for x in ln.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
+            except Exception:
+                continue
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            for nm, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def run_reference_binary(path_in, threads, fmt="lib", out=None, binary=None):
+    from oracle import binding as ob
+    binary = binary or ob.REF_SCALAR
+    out = out or (path_in + ".ref.out")
+    t0 = time.perf_counter()
+    cp = ob.run_reference(binary, ["-i", path_in, "-j", str(threads), "-o", fmt, "-w", out])
+    dt = time.perf_counter() - t0
+    if cp.returncode != 0:
+        raise RuntimeError("reference binary failed: " + cp.stderr.decode()[-500:])
+    return dt, out
+
+
+def reference_arm(args, rank, world):
+    """Times the unmodified reference binary on the host cores: rank 0 only, bounded sample per step."""
+    if rank != 0:
+        return 0
+    from oracle import binding as ob
+    w, files = make_workload(args.workload, args.nseq)
+    m = min(SAMPLE_SEQS_CPU, w["n"])
+    sample = subset_file(files[0], m, files[0] + ".sample." + w["fmt"]) if m < w["n"] else files[0]
+    cores = os.cpu_count()
+    n_pairs = m * (m - 1) // 2
+    if not os.path.exists(ob.REF_SCALAR):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/lara_scalar missing (build on a box with /root/reference)"}))
+        return 0
+    for _ in range(args.warmup):
+        run_reference_binary(sample, cores)
+    times = []
+    for _ in range(args.steps):
+        dt, _ = run_reference_binary(sample, cores)
+        times.append(dt)
+    t = sum(times)
+    value = n_pairs * args.steps / t
+    cells = n_pairs * 500.0 * w["length"] * w["length"]
+    line = {
+        "impl": "reference", "metric": "aligned pairs/s", "value": value, "unit": "pairs/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": workload_config(args, w, world),
+        "gcups_upper_bound": cells * args.steps / t / 1e9,
+        "cpu_baseline": {"value": value, "unit": "pairs/s", "cores": cores, "kind": "reference",
+                         "sample": "first %d of the %d sequences (%d pairs, all iterations), lara_scalar -j %d, process wall clock incl. parse+write"
+                                   % (m, w["n"], n_pairs, cores)},
+        "e2e": {"value": value, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, w, world):
+    return {"workload": "%s: %d synthetic RNAs x %d nt %s, all %d pairs, 500 iterations (BASELINE.json configs[%d])"
+                        % (args.workload, w["n"], w["length"], w["fmt"], w["n"] * (w["n"] - 1) // 2,
+                           {"c1": 0, "c2": 1, "c3": 2}[args.workload]),
+            "n_sequences": w["n"], "length": w["length"], "pairs": w["n"] * (w["n"] - 1) // 2,
+            "num_iterations": 500, "partition": "round-robin over the length-sorted pair list, %d rank(s)" % world,
+            "l2": "per-batch working set (trace + multipliers) is larger than L2; no explicit flush"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--nseq", type=int, default=0, help="developer switch: only the first NSEQ sequences")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+
+    import numpy as np
+    import torch
+    import lara_b200 as lb
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the hot path has no CPU fallback")
+    multi_proc = world > 1
+    if multi_proc:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        device_ids = [local_rank]
+    else:
+        torch.cuda.set_device(0)
+        device_ids = list(range(max(1, args.gpus)))       # one process driving N GPUs through the C ABI (-j N)
+
+    def barrier():
+        if multi_proc:
+            dist.barrier()
+        for d in device_ids:
+            torch.cuda.synchronize(d)
+
+    def reduce_max(x):
+        if not multi_proc:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def reduce_sum(x):
+        if not multi_proc:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    w, files = make_workload(args.workload, args.nseq)
+    store = lb.InputStorage.from_files(in_file=files[0])
+    flat = store.flat()
+    n = len(store)
+    lens = store.lengths()
+    ia, ib = np.triu_indices(n, k=1)
+    # length-sorted (longest first) global order, dealt round-robin to the ranks
+    cost = np.maximum(lens[ia], lens[ib]) * 100000 + np.minimum(lens[ia], lens[ib])
+    order = np.argsort(-cost, kind="stable")
+    mine = order[rank::world] if multi_proc else order
+    my_a, my_b = ia[mine].astype(np.int32), ib[mine].astype(np.int32)
+    n_pairs_total = len(ia)
+
+    params = lb.Parameters()
+    ctx = lb.Context(params, device_ids=device_ids)
+    ctx.set_sequences(flat)
+    ctx.prepare_pairs(my_a, my_b)
+
+    for _ in range(args.warmup):
+        ctx.run_prepared()
+
+    sampler = ClockSampler(device_ids[0])
+    barrier()
+    if rank == 0:
+        sampler.start()
+    dev_ms = 0.0
+    dp_ms = post_ms = setup_ms = 0.0
+    cells = 0
+    launches = dp_launches = 0
+    wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        ctx.run_prepared()
+        st = ctx.stats()
+        dev_ms += st.ms_device
+        dp_ms += st.ms_dp
+        post_ms += st.ms_bounds
+        setup_ms += st.ms_setup
+        cells += st.dp_cells
+        launches += st.kernel_launches
+        dp_launches += st.dp_launches
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - wall0)
+    clocks = sampler.stop() if rank == 0 else None
+    t_ms = reduce_max(dev_ms)
+    wall_ms = reduce_max(wall_ms)
+    cells_all = reduce_sum(float(cells))
+    launches_all = int(reduce_sum(float(launches)))
+    value = n_pairs_total * args.steps / (t_ms * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers ----------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        barrier()
+        t0 = time.perf_counter()
+        h2d = d2h = 0
+        e2e_steps = max(1, min(args.steps, 2))
+        for _ in range(e2e_steps):
+            ctx.set_sequences(flat)
+            res = ctx.solve_pairs(my_a, my_b)
+            st = ctx.stats()
+            h2d += st.h2d_bytes + 8 * len(my_a)
+            d2h += st.d2h_bytes
+            ctx.free(res)
+        barrier()
+        e2e_s = reduce_max(time.perf_counter() - t0)
+        e2e = {"value": n_pairs_total * e2e_steps / e2e_s, "unit": "pairs/s",
+               "h2d_bytes_per_step": int(reduce_sum(float(h2d)) / e2e_steps),
+               "d2h_bytes_per_step": int(reduce_sum(float(d2h)) / e2e_steps), "steps": e2e_steps,
+               "timing": "host wall clock around lara_gpu_set_sequences + lara_gpu_solve_pairs (results in host memory)"}
+
+    if rank != 0:
+        ctx.close()
+        if multi_proc:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel (DP fill) ------------------------------------------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    int_rates = {k: ctx.int_issue_rate(k) for k in (0, 1, 2)}
+    int_peak = max(int_rates.values())
+    dp_cells_rank0 = float(cells)
+    achieved_gops = dp_cells_rank0 * OPS_PER_CELL / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else 0.0
+    st = ctx.stats()
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    roofline = {
+        "kernel": "gotoh_fill_kernel", "bound": "int32_issue", "achieved": achieved_gops, "peak": int_peak,
+        "unit": "Gop/s", "frac": achieved_gops / int_peak if int_peak else None,
+        "peak_source": "measured on this GPU: lara_gpu_int_issue_rate (IADD %.0f, LOP3+VIMNMX %.0f, DP mix %.0f Gop/s)"
+                       % (int_rates[0], int_rates[1], int_rates[2]),
+        "ops_per_cell": OPS_PER_CELL, "dp_gcups_kernel_only": dp_cells_rank0 / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else None,
+        "dp_launches": dp_launches, "dp_ms_per_launch": dp_ms / dp_launches if dp_launches else None,
+        "traffic": None,
+        "hbm": {"algorithmic_bytes_per_cell": 1.3, "achieved_gbs": dp_cells_rank0 * 1.3 / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else None,
+                "peak_gbs": hbm_peak, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+        "share_of_step": {"dp": dp_ms / dev_ms if dev_ms else None, "post": post_ms / dev_ms if dev_ms else None,
+                          "setup": setup_ms / dev_ms if dev_ms else None},
+    }
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        try:
+            roofline["traffic"] = json.load(open(prof)).get("gotoh_fill_kernel_dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    # ---- CPU baseline: the unmodified reference binary on a bounded sample -----------------------------
+    cpu = None
+    if not args.no_cpu_baseline and not multi_proc and args.gpus == 1:
+        from oracle import binding as ob
+        m = min(SAMPLE_SEQS_CPU, n)
+        sample = subset_file(files[0], m, files[0] + ".sample." + w["fmt"]) if m < n else files[0]
+        cores = os.cpu_count()
+        if os.path.exists(ob.REF_SCALAR):
+            dt, ref_out = run_reference_binary(sample, cores)
+            mp = m * (m - 1) // 2
+            # live parity check on the same sample: GPU library vs reference binary, written output byte for byte
+            s2 = lb.InputStorage.from_files(in_file=sample)
+            ctx2 = lb.Context(params, device_ids=[device_ids[0]])
+            out2 = lb.OutputLibrary(s2, "lib")
+            lb.solve(out2, s2, params, ctx=ctx2)
+            mine_out = sample + ".gpu.out"
+            out2.print(mine_out)
+            same = open(mine_out, "rb").read() == open(ref_out, "rb").read()
+            out2._release()
+            ctx2.close()
+            cpu = {"value": mp / dt, "unit": "pairs/s", "cores": cores, "kind": "reference",
+                   "sample": "first %d of the %d sequences (%d pairs, all 500 iterations), oracle/_ref/lara_scalar -j %d, "
+                             "process wall clock %.1f s incl. parse+write" % (m, n, mp, cores, dt),
+                   "output_identical_to_gpu_on_sample": bool(same)}
+        else:
+            cpu = {"value": None, "unit": "pairs/s", "cores": cores, "kind": "reference",
+                   "sample": "oracle/_ref/lara_scalar not present on this box"}
+
+    line = {
+        "metric": "aligned pairs/s", "value": value, "unit": "pairs/s", "n_gpus": max(world, args.gpus),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+        "config": workload_config(args, w, max(world, args.gpus)),
+        "gcups": cells_all / (t_ms * 1e-3) / 1e9, "wall_ms_per_step": wall_ms / args.steps,
+        "clocks": clocks, "e2e": e2e, "gpu_launches": launches_all, "roofline": roofline, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    ctx.close()
+    if multi_proc:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -121,7 +121,8 @@ typedef struct lara_stats
     int64_t sum_iterations;
     int64_t n_active_edges;    /* sum of E                                              */
     int64_t n_interactions;    /* sum of D (dual dimension)                             */
-    int64_t reserved[8];
+    double  ms_device;         /* CUDA-event span of the solve on the library's stream (max over devices) */
+    int64_t reserved[7];
 } lara_stats;
 
 typedef struct lara_ctx lara_ctx;

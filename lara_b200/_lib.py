@@ -74,7 +74,8 @@ class LaraStats(C.Structure):
         ("sum_iterations", C.c_int64),
         ("n_active_edges", C.c_int64),
         ("n_interactions", C.c_int64),
-        ("reserved", C.c_int64 * 8),
+        ("ms_device", C.c_double),
+        ("reserved", C.c_int64 * 7),
     ]
 
 

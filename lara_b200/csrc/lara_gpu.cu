@@ -52,6 +52,7 @@ struct Device
     int32_t * dActive = nullptr;
     int32_t * hActive = nullptr;            // pinned
     std::vector<cudaEvent_t> events;
+    cudaEvent_t evRun0 = nullptr, evRun1 = nullptr;     // span of one run_device on the stream
     // share of the prepared pair list and its device-resident outputs
     std::vector<OrientedPair> pairs;
     PairOutHdr * dOutHdr = nullptr;
@@ -361,6 +362,7 @@ void run_device(lara_ctx & ctx, Device & dv)
     {
         CK(cudaSetDevice(dv.id));
         std::memset(&dv.stats, 0, sizeof(dv.stats));
+        CK(cudaEventRecord(dv.evRun0, dv.stream));
         size_t begin = 0;
         while (begin < dv.pairs.size())
         {
@@ -368,7 +370,9 @@ void run_device(lara_ctx & ctx, Device & dv)
             run_batch(ctx, dv, begin, end);
             begin = end;
         }
+        CK(cudaEventRecord(dv.evRun1, dv.stream));
         CK(cudaStreamSynchronize(dv.stream));
+        dv.stats.ms_device = ev_ms(dv.evRun0, dv.evRun1);
     }
     catch (std::exception const & e)
     {
@@ -456,6 +460,8 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
                 CK(cudaEventCreate(&ev));
                 dv.events.push_back(ev);
             }
+            CK(cudaEventCreate(&dv.evRun0));
+            CK(cudaEventCreate(&dv.evRun1));
             CK(post_configure_device());
             // keep freed blocks in the stream-ordered pool between batches
             cudaMemPool_t pool;
@@ -487,6 +493,8 @@ void lara_gpu_destroy(lara_ctx * ctx)
         cudaFree(dv.dActive);
         if (dv.hActive) cudaFreeHost(dv.hActive);
         for (cudaEvent_t ev : dv.events) cudaEventDestroy(ev);
+        if (dv.evRun0) cudaEventDestroy(dv.evRun0);
+        if (dv.evRun1) cudaEventDestroy(dv.evRun1);
         if (dv.stream) cudaStreamDestroy(dv.stream);
     }
     delete ctx;
@@ -631,6 +639,7 @@ int lara_gpu_run_prepared(lara_ctx * ctx)
         agg.ms_setup = std::max(agg.ms_setup, dv.stats.ms_setup);
         agg.ms_dp = std::max(agg.ms_dp, dv.stats.ms_dp);
         agg.ms_bounds = std::max(agg.ms_bounds, dv.stats.ms_bounds);
+        agg.ms_device = std::max(agg.ms_device, dv.stats.ms_device);
         agg.dp_cells += dv.stats.dp_cells; agg.dp_launches += dv.stats.dp_launches;
         agg.kernel_launches += dv.stats.kernel_launches; agg.filter_cells += dv.stats.filter_cells;
         agg.n_pairs += dv.stats.n_pairs; agg.sum_iterations += dv.stats.sum_iterations;
