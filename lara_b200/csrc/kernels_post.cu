@@ -447,7 +447,9 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
     // ---- 5. primal value, best structural alignment (:412-421) -----------------------------------
     int32_t const primal = lbSeq + lbStruct + gapScore;
-    bool const improved = primal > st.bestScore;
+    // one lane decides and broadcasts: lane 0 overwrites st.bestScore below, and a lane that runs late must
+    // not compare against the new value
+    bool const improved = __shfl_sync(kFull, (lane == 0 && primal > st.bestScore) ? 1 : 0, 0) != 0;
     if (improved)
     {
         for (int i = lane; i < nLines; i += 32)

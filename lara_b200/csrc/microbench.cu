@@ -26,7 +26,7 @@ __global__ void int_issue_kernel(int iters, int32_t * out)
             #pragma unroll
             for (int i = 0; i < 8; ++i)
             {
-                if (KIND == 0) a[i] = a[i] + b + it;                       // IADD3 / IMAD.IADD
+                if (KIND == 0) a[i] = a[i] + a[(i + 3) & 7];               // IADD3 (two live operands: cannot be folded)
                 else if (KIND == 1) a[i] = max(a[i] ^ it, b);               // LOP3 + VIMNMX
                 else
                 {   // the DP's decision step: difference, max, funnel shift
