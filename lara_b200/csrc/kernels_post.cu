@@ -79,6 +79,7 @@ struct WarpSmem
     uint8_t * matched;      // [maxLb]
     unsigned long long * cand;  // [smemCand]
     int32_t * misc;         // [16]: 0 nList, 1 nCand, 2 matchScore, 3..10 selection weights, 11 error
+    uint32_t * win;         // [128] traceback window: 32 rows x 32 nibbles
 };
 
 __device__ __forceinline__ uint32_t trace_nibble(int32_t const * __restrict__ tr, int R, int W, int nSteps, int c, int r)
@@ -100,50 +101,131 @@ __device__ __forceinline__ uint32_t seqan_tv(uint32_t nib)
     return tv;
 }
 
-// Traceback + evaluateLines by one thread.  Returns number of lines; lines in reverse order.
+// Traceback + evaluateLines, warp-cooperative and warp-uniform.
+// The trace of the 32 x 32 cell window whose bottom-right corner is the walker's position is fetched by all
+// lanes at once (lane i packs the nibbles of window row r - i into four words of shared memory: one round
+// trip to L2/HBM per window instead of one per step).  Inside the window the walk advances by SEGMENTS, each
+// found with one ballot over the 32 lanes:
+//   S     lane i looks at the diagonal cell (c - i, r - i); the leading lanes whose cell took the diagonal are
+//         one run of matches (_doTraceback, dp_traceback_impl.h:376-418) and write their lines in parallel;
+//   VRUN  lane i looks at (c, r - i): `while ((tv & 4) && r != 1) step; step` of _doTracebackMaxFromVertical
+//         (:223-264) = the leading lanes whose cell extended V, plus the opening step;
+//   HRUN  lane i looks at (c - i, r), symmetric (:302-341).
+// All lanes carry the same (c, r, state).  Returns the number of lines; lines in reverse order in linesRev;
+// gapOut = gap score of evaluateLines (src/lagrange.hpp:147-221).
 __device__ int traceback_walk(PairDesc const & d, PairState const & st, int32_t const * __restrict__ arena,
-                              int32_t go, int32_t ge, uint32_t * linesRev, int32_t & gapOut)
+                              int32_t go, int32_t ge, uint32_t * linesRev, uint32_t * win, int32_t & gapOut, int lane)
 {
     int32_t const * __restrict__ tr = arena + d.offTrace;
     int const R = d.R, W = d.W, nSteps = d.nSteps;
     int c = d.la, r = d.lb;
-    uint32_t tv = seqan_tv(trace_nibble(tr, R, W, nSteps, c, r));
-    // _correctTraceValue (dp_algorithm_impl.h:1168-1185) then _retrieveInitialTraceDirection
-    // (dp_traceback_impl.h:456-483, PreferGapsAtEnd_): gaps are preferred at the end cell on ties.
-    if (st.vEnd == st.sEnd) tv = (tv & (4u | 16u)) | 64u;
-    else if (st.hEnd == st.sEnd) tv = (tv & (2u | 8u)) | 32u;
-    else if (tv & 64u) tv &= (4u | 16u | 64u);
-    else if (tv & 32u) tv &= (2u | 8u | 32u);
     int n = 0;
     int32_t gap = 0;
     int prev = 0;                       // 0 match, 1 vertical (gap in A), 2 horizontal (gap in B)
-    auto fetch = [&]() -> uint32_t { return (c > 0 && r > 0) ? seqan_tv(trace_nibble(tr, R, W, nSteps, c, r)) : 0u; };
-    auto stepV = [&]() { gap += (prev == 1) ? ge : go; prev = 1; --r; };
-    auto stepH = [&]() { gap += (prev == 2) ? ge : go; prev = 2; --c; };
+    int state = 0;                      // 0 S, 1 VRUN, 2 HRUN
+    // end cell: _correctTraceValue (dp_algorithm_impl.h:1168-1185) + _retrieveInitialTraceDirection
+    // (dp_traceback_impl.h:456-483, PreferGapsAtEnd_): 1 = forced vertical, 2 = forced horizontal
+    int endFix = (st.vEnd == st.sEnd) ? 1 : ((st.hEnd == st.sEnd) ? 2 : 0);
+    bool first = true;
     while (c > 0 && r > 0)
     {
-        if (tv & 1u)
+        // ---- window rows [r-31, r], columns [c-31, c] --------------------------------------------
+        int const cHi = c, rHi = r;
         {
-            --c; --r; prev = 0;
-            linesRev[n++] = ((uint32_t)c << 16) | (uint32_t)r;
-            tv = fetch();
+            int const rr = rHi - lane;
+            uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = 0;
+            if (rr >= 1)
+            {
+                int const k = (rr - 1) / R, j = (rr - 1) - k * R;
+                int const wj = j >> 3;
+                int const nInWord = min(8, R - 8 * wj);
+                int const sh = 4 * (nInWord - 1 - (j & 7));
+                int32_t const * __restrict__ src = tr + (size_t)k * ((size_t)nSteps * W) + wj;
+                int const tHi = cHi - 1 + k;                    // step of column cHi in strip k
+                #pragma unroll
+                for (int x = 0; x < 32; ++x)                    // window column x <-> matrix column cHi - x
+                {
+                    int const t = tHi - x;
+                    uint32_t nib = 0;
+                    if (cHi - x >= 1)
+                        nib = ((uint32_t)__ldg(src + (size_t)t * W) >> sh) & 15u;
+                    if (x < 8) w0 |= nib << (4 * x);
+                    else if (x < 16) w1 |= nib << (4 * (x - 8));
+                    else if (x < 24) w2 |= nib << (4 * (x - 16));
+                    else w3 |= nib << (4 * (x - 24));
+                }
+            }
+            __syncwarp();
+            *reinterpret_cast<uint4 *>(win + 4 * lane) = make_uint4(w0, w1, w2, w3);
+            __syncwarp();
         }
-        else if ((tv & 64u) && (tv & 4u))
+        while (c > 0 && r > 0 && cHi - c < 32 && rHi - r < 32)
         {
-            while ((tv & 4u) && r != 1) { stepV(); tv = fetch(); }
-            stepV(); tv = fetch();
+            int const rho = rHi - r, x = cHi - c;
+            if (state == 0)
+            {
+                int const ri = rho + lane, xi = x + lane;
+                bool const inw = ri < 32 && xi < 32 && c - lane >= 1 && r - lane >= 1;
+                uint32_t nib = inw ? ((win[4 * ri + (xi >> 3)] >> (4 * (xi & 7))) & 15u) : 0u;
+                if (first && lane == 0)
+                {
+                    if (endFix == 1) nib = (nib | kTrGap) & ~kTrFromH;
+                    else if (endFix == 2) nib = nib | kTrGap | kTrFromH;
+                }
+                first = false;
+                unsigned const diagMask = __ballot_sync(kFull, inw && !(nib & kTrGap));
+                int const run = (diagMask == kFull) ? 32 : (__ffs(~diagMask) - 1);
+                if (run > 0)
+                {
+                    if (lane < run)
+                        linesRev[n + lane] = ((uint32_t)(c - lane - 1) << 16) | (uint32_t)(r - lane - 1);
+                    n += run; c -= run; r -= run; prev = 0;
+                    continue;
+                }
+                // lane 0's cell (always inside the window) took a gap: enter the run at this same cell
+                uint32_t const nib0 = __shfl_sync(kFull, nib, 0);
+                state = (nib0 & kTrFromH) ? 2 : 1;
+            }
+            if (state == 1)
+            {
+                int const ri = rho + lane;
+                bool const inw = ri < 32 && r - lane >= 1;
+                uint32_t const nib = inw ? ((win[4 * ri + (x >> 3)] >> (4 * (x & 7))) & 15u) : 0u;
+                unsigned const extMask = __ballot_sync(kFull, inw && !(nib & kTrVOpen) && (r - lane) != 1);
+                int const m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                // the cell that ends the run is lane m's; if it lies outside the window, stay in the run
+                bool const closes = m < 32 && rho + m < 32;
+                int const steps = closes ? m + 1 : m;
+                if (steps > 0)
+                {
+                    gap += ((prev == 1) ? ge : go) + (steps - 1) * ge;
+                    prev = 1;
+                    r -= steps;
+                }
+                state = closes ? 0 : 1;
+            }
+            else
+            {
+                int const xi = x + lane;
+                bool const inw = xi < 32 && c - lane >= 1;
+                uint32_t const nib = inw ? ((win[4 * rho + (xi >> 3)] >> (4 * (xi & 7))) & 15u) : 0u;
+                unsigned const extMask = __ballot_sync(kFull, inw && !(nib & kTrHOpen) && (c - lane) != 1);
+                int const m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                bool const closes = m < 32 && x + m < 32;
+                int const steps = closes ? m + 1 : m;
+                if (steps > 0)
+                {
+                    gap += ((prev == 2) ? ge : go) + (steps - 1) * ge;
+                    prev = 2;
+                    c -= steps;
+                }
+                state = closes ? 0 : 2;
+            }
         }
-        else if ((tv & 64u) && (tv & 16u)) { stepV(); tv = fetch(); }
-        else if ((tv & 32u) && (tv & 2u))
-        {
-            while ((tv & 2u) && c != 1) { stepH(); tv = fetch(); }
-            stepH(); tv = fetch();
-        }
-        else if ((tv & 32u) && (tv & 8u)) { stepH(); tv = fetch(); }
-        else break;
     }
-    while (r > 0) stepV();              // leading gaps (dp_traceback_impl.h:541-544)
-    while (c > 0) stepH();
+    // leading gaps (dp_traceback_impl.h:541-544): vertical first, then horizontal
+    if (r > 0) { gap += ((prev == 1) ? ge : go) + (r - 1) * ge; prev = 1; }
+    if (c > 0) { gap += ((prev == 2) ? ge : go) + (c - 1) * ge; prev = 2; }
     gapOut = gap;
     return n;
 }
@@ -304,13 +386,15 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
     // carve the per-warp shared memory
     size_t const candBytes = (size_t)smemCand * 8;
-    size_t const perWarp = candBytes + 64 + (size_t)maxLb * 8 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    size_t const lb4 = ((size_t)maxLb * 4 + 15) / 16 * 16;
+    size_t const perWarp = candBytes + 64 + 512 + 2 * lb4 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
     unsigned char * base = smemRaw + (size_t)warpInBlock * perWarp;
     WarpSmem sm;
     sm.cand = (unsigned long long *)base;                     base += candBytes;
     sm.misc = (int32_t *)base;                                base += 64;
-    sm.linesRev = (uint32_t *)base;                           base += (size_t)maxLb * 4;
-    sm.curE = (int32_t *)base;                                base += (size_t)maxLb * 4;
+    sm.win = (uint32_t *)base;                                base += 512;
+    sm.linesRev = (uint32_t *)base;                           base += lb4;
+    sm.curE = (int32_t *)base;                                base += lb4;
     sm.lineOfA = (int16_t *)base;                             base += ((size_t)maxLa * 2 + 15) / 16 * 16;
     sm.matched = (uint8_t *)base;
 
@@ -318,15 +402,9 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     (void)lb;
 
     // ---- 1. traceback + evaluateLines ------------------------------------------------------------
-    int nLines = 0;
     int32_t gapScore = 0;
-    if (lane == 0)
-    {
-        nLines = traceback_walk(d, st, arena, P.go, P.ge, sm.linesRev, gapScore);
-        sm.misc[0] = 0; sm.misc[1] = 0; sm.misc[2] = 0; sm.misc[11] = 0;
-    }
-    nLines = __shfl_sync(kFull, nLines, 0);
-    gapScore = __shfl_sync(kFull, gapScore, 0);
+    int const nLines = traceback_walk(d, st, arena, P.go, P.ge, sm.linesRev, sm.win, gapScore, lane);
+    if (lane == 0) { sm.misc[0] = 0; sm.misc[1] = 0; sm.misc[2] = 0; sm.misc[11] = 0; }
     for (int a = lane; a < la; a += 32) sm.lineOfA[a] = -1;
     __syncwarp();
     if (kTracebackOnly)
@@ -571,7 +649,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
 size_t post_smem_per_warp(int maxLa, int maxLb, int smemCand)
 {
-    return (size_t)smemCand * 8 + 64 + (size_t)maxLb * 8 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    return (size_t)smemCand * 8 + 64 + 512 + 2 * (((size_t)maxLb * 4 + 15) / 16 * 16) + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
 }
 
 } // namespace
