@@ -35,7 +35,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 OPS_PER_CELL = 9.0          # 5 IADD + 4 tie-aware maxima
-SAMPLE_SEQS_CPU = 24        # cpu_baseline / reference arm: first 24 of the workload's sequences (276 pairs)
+SAMPLE_SEQS_CPU = 48        # cpu_baseline / reference arm: first 48 of the workload's sequences (1,128 pairs)
 
 WORKLOADS = {
     "c1": dict(seed=1, n=10, length=120, fmt="dbn"),
@@ -251,11 +251,11 @@ def main():
     flat = store.flat()
     n = len(store)
     lens = store.lengths()
-    ia, ib = np.triu_indices(n, k=1)
+    from lara_b200 import partition
+    ia, ib = partition.all_pairs(n)
     # length-sorted (longest first) global order, dealt round-robin to the ranks
-    cost = np.maximum(lens[ia], lens[ib]) * 100000 + np.minimum(lens[ia], lens[ib])
-    order = np.argsort(-cost, kind="stable")
-    mine = order[rank::world] if multi_proc else order
+    order = partition.cost_order(lens, ia, ib)
+    mine = partition.shard(order, rank, world) if multi_proc else order
     my_a, my_b = ia[mine].astype(np.int32), ib[mine].astype(np.int32)
     n_pairs_total = len(ia)
 

@@ -40,3 +40,40 @@ def random_pssm(rng, n, la, lb, density=0.3, lo=-20000, hi=60000):
     mask = rng.random((n, la, lb)) < density
     p[~mask] = -1431655764
     return p
+
+
+# ---- golden fixtures (tests/golden/manifest.json: outputs of the unmodified reference binaries) ----------
+def golden_cases():
+    import json
+    with open(os.path.join(GOLDEN, "manifest.json")) as f:
+        return json.load(f)["cases"]
+
+
+def golden_setup(case):
+    """-> (Parameters, InputStorage) for one manifest entry, parsed by the host CLI mirror exactly like the
+    reference parsed its command line."""
+    import lara_b200 as lb
+    files = [os.path.join(GOLDEN, f) for f in case["files"]]
+    argv = []
+    if case["format"] == "dp":
+        for f in files:
+            argv += ["-d", f]
+    else:
+        argv += ["-i", files[0]]
+    argv += list(case["options"])
+    if case["build"] == "simd":
+        argv += ["-g", "1"]
+    p = lb.Parameters(argv)
+    assert p.status == lb.Parameters.CONTINUE
+    return p, lb.InputStorage(p)
+
+
+def write_results(store, res, fmt):
+    """lara_output_write into a temp file -> bytes."""
+    import ctypes as C
+    from lara_b200 import _lib
+    out = os.path.join(tempfile.mkdtemp(prefix="lara_o_"), "out.txt")
+    rc = _lib.load().lara_output_write(store._h, C.byref(res), fmt.encode(), out.encode())
+    assert rc == 0, _lib.load().lara_host_last_error()
+    with open(out, "rb") as f:
+        return f.read()
