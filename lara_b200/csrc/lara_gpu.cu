@@ -11,7 +11,9 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <deque>
 #include <map>
 #include <mutex>
 #include <stdexcept>
@@ -41,17 +43,32 @@ struct OrientedPair
     int64_t request;            // position in the caller's pair list
 };
 
+// One host worker of a device: its own stream, events and live-pair counter.  Several workers run batches
+// concurrently so that the issue-bound DP kernel of one batch overlaps the latency-bound post kernel of another
+// and finished pairs of one batch leave room for the blocks of the others.
+struct Worker
+{
+    cudaStream_t stream = nullptr;
+    int32_t * dActive = nullptr;
+    int32_t * hActive = nullptr;            // pinned
+    std::vector<cudaEvent_t> events;
+    cudaEvent_t evDone = nullptr;
+    lara_stats stats{};
+    std::string err;
+};
+
 // All device-side resources of one GPU.
 struct Device
 {
     int id = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;          // == workers[0].stream
+    std::vector<Worker> workers;
+    std::mutex queueMutex;
+    size_t nextBegin = 0;                   // next unassigned pair of `pairs`
     DevInputs in{};
     void * dSeq = nullptr, * dSeqOff = nullptr, * dBpPartner = nullptr, * dBpWeight = nullptr, * dBpOff = nullptr;
     int32_t * negBuf = nullptr;
-    int32_t * dActive = nullptr;
-    int32_t * hActive = nullptr;            // pinned
-    std::vector<cudaEvent_t> events;
+    std::vector<cudaEvent_t> events;        // two scratch events for copies / microbenchmarks
     cudaEvent_t evRun0 = nullptr, evRun1 = nullptr;     // span of one run_device on the stream
     // share of the prepared pair list and its device-resident outputs
     std::vector<OrientedPair> pairs;
@@ -71,7 +88,9 @@ struct lara_ctx
     lara_params P{};
     DevParams dp{};
     std::string err;
-    std::vector<Device> devs;
+    std::deque<Device> devs;                // deque: Device holds a mutex and is not movable
+    int nWorkers = 3;                       // concurrent batches per device (env LARA_B200_WORKERS)
+    size_t batchPairsDefault = 8192;        // pairs per batch (env LARA_B200_BATCH)
     // host copy of the inputs (for pair orientation and batch sizing)
     int32_t nSeq = 0;
     std::vector<int64_t> seqOff, bpOff;
@@ -150,11 +169,11 @@ double ev_ms(cudaEvent_t a, cudaEvent_t b)
 // ---------------------------------------------------------------------------------------------------
 // One batch: pairs [begin, end) of dv.pairs (already length sorted).
 // ---------------------------------------------------------------------------------------------------
-void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
+void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t end)
 {
     int const n = (int)(end - begin);
     DevParams const & dp = ctx.dp;
-    cudaStream_t const s = dv.stream;
+    cudaStream_t const s = wk.stream;
     std::vector<PairDesc> desc((size_t)n);
     int maxLa = 0, maxLb = 0, maxK = 0;
     // ---- stage A layout: everything that only depends on the lengths -----------------------------
@@ -206,13 +225,13 @@ void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
     CK(cudaMemsetAsync(dState, 0, sizeof(PairState) * (size_t)n, s));
     CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
 
-    cudaEvent_t evS0 = dv.events[0], evS1 = dv.events[1];
+    cudaEvent_t evS0 = wk.events[0], evS1 = wk.events[1];
     CK(cudaEventRecord(evS0, s));
     // ---- stage 1: edge filter -> E ------------------------------------------------------------------
     CK(launch_edge_filter(n, dDesc, dState, arena, dv.in, dp, s));
     CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
-    dv.stats.kernel_launches += 1;
+    wk.stats.kernel_launches += 1;
     // ---- stage B layout: per-edge arrays ---------------------------------------------------------------
     int64_t sizeB = 0;
     for (int i = 0; i < n; ++i) sizeB += 4 * align4(std::max(desc[(size_t)i].E, 1)) + align4(desc[(size_t)i].E + 1);
@@ -230,7 +249,7 @@ void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
     CK(launch_setup_count(n, dDesc, dState, arena, dv.in, dp, s));
     CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
-    dv.stats.kernel_launches += 1;
+    wk.stats.kernel_launches += 1;
     int64_t sizeC = 0;
     for (int i = 0; i < n; ++i) sizeC += 6 * align4(std::max(desc[(size_t)i].D, 1)) + align4(std::max(desc[(size_t)i].nVals, 1));
     Region rC;
@@ -241,13 +260,13 @@ void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
         PairDesc & d = desc[(size_t)i];
         d.offPart = rC.take(d.D); d.offPpos = rC.take(d.D); d.offSc = rC.take(d.D); d.offDual = rC.take(d.D);
         d.offRev = rC.take(d.D); d.offList = rC.take(d.D); d.offVals = rC.take(d.nVals);
-        dv.stats.n_active_edges += d.E; dv.stats.n_interactions += d.D;
-        dv.stats.filter_cells += 2ll * d.la * d.lb;
+        wk.stats.n_active_edges += d.E; wk.stats.n_interactions += d.D;
+        wk.stats.filter_cells += 2ll * d.la * d.lb;
     }
     CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
     // ---- stage 3: fill ---------------------------------------------------------------------------------------
     CK(launch_setup_fill(n, dDesc, dState, arena, dv.in, dp, s));
-    dv.stats.kernel_launches += 1;
+    wk.stats.kernel_launches += 1;
     CK(cudaEventRecord(evS1, s));
 
     // ---- rows-per-lane classes for the DP launches -------------------------------------------------------------
@@ -263,8 +282,8 @@ void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
     int32_t * dIdx = nullptr;
     CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * idxAll.size(), s));
     CK(cudaMemcpyAsync(dIdx, idxAll.data(), sizeof(int32_t) * idxAll.size(), cudaMemcpyHostToDevice, s));
-    *dv.hActive = n;
-    CK(cudaMemcpyAsync(dv.dActive, dv.hActive, sizeof(int32_t), cudaMemcpyHostToDevice, s));
+    *wk.hActive = n;
+    CK(cudaMemcpyAsync(wk.dActive, wk.hActive, sizeof(int32_t), cudaMemcpyHostToDevice, s));
 
     // shared memory candidates: as many as fit next to the line arrays (cap 2048)
     int smemCand = 32;
@@ -273,34 +292,34 @@ void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
     // ---- the subgradient loop -------------------------------------------------------------------------------------
     int const nIter = ctx.P.num_iterations;
     size_t const needEv = 2 + 3 * (size_t)nIter;
-    while (dv.events.size() < needEv)
+    while (wk.events.size() < needEv)
     {
         cudaEvent_t e;
         CK(cudaEventCreate(&e));
-        dv.events.push_back(e);
+        wk.events.push_back(e);
     }
     int itersRun = 0;
     int nextPoll = 1;
     for (int it = 0; it < nIter; ++it)
     {
-        CK(cudaEventRecord(dv.events[2 + 3 * (size_t)it], s));
+        CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it], s));
         for (auto const & c : cls)
         {
             CK(launch_gotoh_fill(std::get<0>(c), std::get<2>(c), dIdx + std::get<1>(c), dDesc, dState, arena, dv.negBuf,
                                  dp.go, dp.ge, s));
-            dv.stats.kernel_launches += 1; dv.stats.dp_launches += 1;
+            wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
         }
-        CK(cudaEventRecord(dv.events[2 + 3 * (size_t)it + 1], s));
+        CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 1], s));
         CK(launch_iterate_post(n, dDesc, dState, arena, dp, dv.dOutHdr + begin, dv.dOutLines, dv.dOutOff + begin,
-                               dv.dActive, maxLa, maxLb, smemCand, s));
-        dv.stats.kernel_launches += 1;
-        CK(cudaEventRecord(dv.events[2 + 3 * (size_t)it + 2], s));
+                               wk.dActive, maxLa, maxLb, smemCand, s));
+        wk.stats.kernel_launches += 1;
+        CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 2], s));
         itersRun = it + 1;
         if (it + 1 == nextPoll && it + 1 < nIter)
         {
-            CK(cudaMemcpyAsync(dv.hActive, dv.dActive, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+            CK(cudaMemcpyAsync(wk.hActive, wk.dActive, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
             CK(cudaStreamSynchronize(s));
-            if (*dv.hActive <= 0) break;
+            if (*wk.hActive <= 0) break;
             nextPoll = nextPoll < 16 ? nextPoll * 2 : nextPoll + 16;
         }
     }
@@ -316,16 +335,16 @@ void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
         if (!hState[(size_t)i].done)
             throw std::runtime_error("pair did not finish within numIterations");
         int64_t const its = ctx.P.num_iterations - hState[(size_t)i].remaining;
-        dv.stats.sum_iterations += its;
-        dv.stats.dp_cells += its * (int64_t)desc[(size_t)i].la * desc[(size_t)i].lb;
+        wk.stats.sum_iterations += its;
+        wk.stats.dp_cells += its * (int64_t)desc[(size_t)i].la * desc[(size_t)i].lb;
     }
-    dv.stats.ms_setup += ev_ms(evS0, evS1);
+    wk.stats.ms_setup += ev_ms(evS0, evS1);
     for (int it = 0; it < itersRun; ++it)
     {
-        dv.stats.ms_dp += ev_ms(dv.events[2 + 3 * (size_t)it], dv.events[2 + 3 * (size_t)it + 1]);
-        dv.stats.ms_bounds += ev_ms(dv.events[2 + 3 * (size_t)it + 1], dv.events[2 + 3 * (size_t)it + 2]);
+        wk.stats.ms_dp += ev_ms(wk.events[2 + 3 * (size_t)it], wk.events[2 + 3 * (size_t)it + 1]);
+        wk.stats.ms_bounds += ev_ms(wk.events[2 + 3 * (size_t)it + 1], wk.events[2 + 3 * (size_t)it + 2]);
     }
-    dv.stats.n_pairs += n;
+    wk.stats.n_pairs += n;
     CK(cudaFreeAsync(dIdx, s));
     CK(cudaFreeAsync(rC.ptr, s));
     CK(cudaFreeAsync(rB.ptr, s));
@@ -336,14 +355,14 @@ void run_batch(lara_ctx & ctx, Device & dv, size_t begin, size_t end)
 
 // Pairs per batch from the free device memory and a per-pair estimate (exact for the length dependent
 // part, heuristic for the edge/interaction arrays whose sizes are only known after set-up).
-size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin)
+size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers)
 {
     size_t freeB = 0, totalB = 0;
     cudaMemGetInfo(&freeB, &totalB);
-    double const budget = 0.45 * (double)freeB;
+    double const budget = 0.45 * (double)totalB / (double)nWorkers;
     double used = 0;
     size_t k = begin;
-    size_t const hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : 16384;
+    size_t const hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : ctx.batchPairsDefault;
     while (k < dv.pairs.size() && k - begin < hardCap)
     {
         OrientedPair const & op = dv.pairs[k];
@@ -356,23 +375,72 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin)
     return k;
 }
 
+void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
+{
+    try
+    {
+        CK(cudaSetDevice(dv.id));
+        for (;;)
+        {
+            size_t begin, end;
+            {
+                std::lock_guard<std::mutex> lock(dv.queueMutex);
+                begin = dv.nextBegin;
+                if (begin >= dv.pairs.size()) break;
+                end = batch_limit(ctx, dv, begin, nWorkers);
+                dv.nextBegin = end;
+            }
+            run_batch(ctx, dv, wk, begin, end);
+        }
+        CK(cudaEventRecord(wk.evDone, wk.stream));
+        CK(cudaStreamSynchronize(wk.stream));
+    }
+    catch (std::exception const & e)
+    {
+        wk.err = e.what();
+        cudaGetLastError();
+    }
+}
+
 void run_device(lara_ctx & ctx, Device & dv)
 {
     try
     {
         CK(cudaSetDevice(dv.id));
         std::memset(&dv.stats, 0, sizeof(dv.stats));
+        // few pairs: one worker is enough (and keeps the small-case latency low)
+        int nW = (int)std::min<size_t>((size_t)ctx.nWorkers, (dv.pairs.size() + 2047) / 2048);
+        nW = std::max(1, std::min(nW, (int)dv.workers.size()));
+        dv.nextBegin = 0;
+        for (Worker & wk : dv.workers) { std::memset(&wk.stats, 0, sizeof(wk.stats)); wk.err.clear(); }
         CK(cudaEventRecord(dv.evRun0, dv.stream));
-        size_t begin = 0;
-        while (begin < dv.pairs.size())
+        // the other workers' streams start after the start event
+        for (int w = 1; w < nW; ++w) CK(cudaStreamWaitEvent(dv.workers[(size_t)w].stream, dv.evRun0, 0));
+        if (nW == 1)
+            run_worker(ctx, dv, dv.workers[0], 1);
+        else
         {
-            size_t const end = batch_limit(ctx, dv, begin);
-            run_batch(ctx, dv, begin, end);
-            begin = end;
+            std::vector<std::thread> th;
+            for (int w = 0; w < nW; ++w)
+                th.emplace_back([&ctx, &dv, w, nW]() { run_worker(ctx, dv, dv.workers[(size_t)w], nW); });
+            for (std::thread & t : th) t.join();
         }
+        CK(cudaSetDevice(dv.id));
+        for (int w = 1; w < nW; ++w) CK(cudaStreamWaitEvent(dv.stream, dv.workers[(size_t)w].evDone, 0));
         CK(cudaEventRecord(dv.evRun1, dv.stream));
         CK(cudaStreamSynchronize(dv.stream));
         dv.stats.ms_device = ev_ms(dv.evRun0, dv.evRun1);
+        for (int w = 0; w < nW; ++w)
+        {
+            Worker & wk = dv.workers[(size_t)w];
+            if (!wk.err.empty() && dv.err.empty()) dv.err = wk.err;
+            dv.stats.ms_setup += wk.stats.ms_setup; dv.stats.ms_dp += wk.stats.ms_dp; dv.stats.ms_bounds += wk.stats.ms_bounds;
+            dv.stats.dp_cells += wk.stats.dp_cells; dv.stats.dp_launches += wk.stats.dp_launches;
+            dv.stats.kernel_launches += wk.stats.kernel_launches; dv.stats.filter_cells += wk.stats.filter_cells;
+            dv.stats.n_pairs += wk.stats.n_pairs; dv.stats.sum_iterations += wk.stats.sum_iterations;
+            dv.stats.n_active_edges += wk.stats.n_active_edges; dv.stats.n_interactions += wk.stats.n_interactions;
+        }
+        dv.stats.reserved[0] = nW;
     }
     catch (std::exception const & e)
     {
@@ -433,6 +501,8 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     else
         ids.assign(device_ids, device_ids + n_devices);
     lara_ctx * ctx = new lara_ctx();
+    if (char const * e = std::getenv("LARA_B200_WORKERS")) ctx->nWorkers = std::max(1, std::min(8, std::atoi(e)));
+    if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
     ctx->P = *params;
     ctx->dp = make_dev_params(*params);
     try
@@ -448,12 +518,25 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
             Device & dv = ctx->devs.back();
             dv.id = id;
             CK(cudaSetDevice(id));
-            CK(cudaStreamCreateWithFlags(&dv.stream, cudaStreamNonBlocking));
+            for (int w = 0; w < ctx->nWorkers; ++w)
+            {
+                dv.workers.emplace_back();
+                Worker & wk = dv.workers.back();
+                CK(cudaStreamCreateWithFlags(&wk.stream, cudaStreamNonBlocking));
+                CK(cudaMalloc((void **)&wk.dActive, sizeof(int32_t)));
+                CK(cudaMallocHost((void **)&wk.hActive, sizeof(int32_t)));
+                CK(cudaEventCreateWithFlags(&wk.evDone, cudaEventDisableTiming));
+                for (int k = 0; k < 2; ++k)
+                {
+                    cudaEvent_t ev;
+                    CK(cudaEventCreate(&ev));
+                    wk.events.push_back(ev);
+                }
+            }
+            dv.stream = dv.workers[0].stream;
             CK(cudaMalloc((void **)&dv.negBuf, 64 * sizeof(int32_t)));
             std::vector<int32_t> neg(64, kDpNeg);
             CK(cudaMemcpy(dv.negBuf, neg.data(), 64 * sizeof(int32_t), cudaMemcpyHostToDevice));
-            CK(cudaMalloc((void **)&dv.dActive, sizeof(int32_t)));
-            CK(cudaMallocHost((void **)&dv.hActive, sizeof(int32_t)));
             for (int k = 0; k < 2; ++k)
             {
                 cudaEvent_t ev;
@@ -486,16 +569,21 @@ void lara_gpu_destroy(lara_ctx * ctx)
     for (Device & dv : ctx->devs)
     {
         cudaSetDevice(dv.id);
-        if (dv.stream) cudaStreamSynchronize(dv.stream);
+        for (Worker & wk : dv.workers) if (wk.stream) cudaStreamSynchronize(wk.stream);
         device_free_inputs(dv);
         device_free_outputs(dv);
         cudaFree(dv.negBuf);
-        cudaFree(dv.dActive);
-        if (dv.hActive) cudaFreeHost(dv.hActive);
         for (cudaEvent_t ev : dv.events) cudaEventDestroy(ev);
         if (dv.evRun0) cudaEventDestroy(dv.evRun0);
         if (dv.evRun1) cudaEventDestroy(dv.evRun1);
-        if (dv.stream) cudaStreamDestroy(dv.stream);
+        for (Worker & wk : dv.workers)
+        {
+            cudaFree(wk.dActive);
+            if (wk.hActive) cudaFreeHost(wk.hActive);
+            for (cudaEvent_t ev : wk.events) cudaEventDestroy(ev);
+            if (wk.evDone) cudaEventDestroy(wk.evDone);
+            if (wk.stream) cudaStreamDestroy(wk.stream);
+        }
     }
     delete ctx;
 }
