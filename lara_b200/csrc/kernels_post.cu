@@ -79,7 +79,7 @@ struct WarpSmem
     uint8_t * matched;      // [maxLb]
     unsigned long long * cand;  // [smemCand]
     int32_t * misc;         // [16]: 0 nList, 1 nCand, 2 matchScore, 3..10 selection weights, 11 error
-    uint32_t * win;         // [128] traceback window: 32 rows x 32 nibbles
+    uint32_t * win;         // [256] traceback window (full mode: 32 rows x 32 nibbles; band mode: 8 word rows x L)
 };
 
 __device__ __forceinline__ uint32_t trace_nibble(int32_t const * __restrict__ tr, int R, int W, int nSteps, int c, int r)
@@ -224,6 +224,189 @@ __device__ int traceback_walk(PairDesc const & d, PairState const & st, int32_t 
         }
     }
     // leading gaps (dp_traceback_impl.h:541-544): vertical first, then horizontal
+    if (r > 0) { gap += ((prev == 1) ? ge : go) + (r - 1) * ge; prev = 1; }
+    if (c > 0) { gap += ((prev == 2) ? ge : go) + (c - 1) * ge; prev = 2; }
+    gapOut = gap;
+    return n;
+}
+
+// ---- band mode (kernels_band.cu) ---------------------------------------------------------------------------
+// Trace decisions of ANY cell of the matrix: inside the band from the stored nibbles, outside from the closed
+// forms of the pure gap regions U (c - r > dHi) and L (c - r < dLo); see tools/band_proto.py (u_nib / l_nib).
+struct BandView
+{
+    int la, lb, dLo, dHi, L;
+    int32_t go, ge;
+    int32_t const * trace;
+    int32_t const * uTH, * uTS, * uM;      // per row
+    int32_t const * lTV, * lTS, * lM;      // per column
+};
+
+__device__ __forceinline__ int32_t band_uV(BandView const & v, int c, int r)
+{
+    return r == 0 ? kBandNeg : (c + r - 1) * v.ge + v.go + v.uM[r];
+}
+__device__ __forceinline__ int32_t band_uH(BandView const & v, int c, int r)
+{
+    int32_t const t = max(v.uTH[r], v.uTS[r]);
+    bool const first = (c == r + v.dHi + 1) || r == 0;
+    return c * v.ge + (first ? t : max(t, v.uM[r] + 2 * v.go + (r - 2) * v.ge));
+}
+__device__ __forceinline__ int32_t band_lH(BandView const & v, int c, int r)
+{
+    return c == 0 ? kBandNeg : (c + r - 1) * v.ge + v.go + v.lM[c];
+}
+__device__ __forceinline__ int32_t band_lV(BandView const & v, int c, int r)
+{
+    int32_t const t = max(v.lTV[c], v.lTS[c]);
+    bool const first = (r == c - v.dLo + 1) || c == 0;
+    return r * v.ge + (first ? t : max(t, v.lM[c] + 2 * v.go + (c - 2) * v.ge));
+}
+// nibble of a cell outside the band (c >= 1, r >= 1): the diagonal never wins there
+__device__ uint32_t band_outside_nib(BandView const & v, int c, int r)
+{
+    uint32_t nib = kTrGap;
+    if (c - r > v.dHi)
+    {
+        int32_t const hCur = band_uH(v, c, r), vCur = band_uV(v, c, r);
+        if (c == r + v.dHi + 1) { if (v.uTH[r] < v.uTS[r]) nib |= kTrHOpen; }
+        else
+        {
+            int32_t const hl = band_uH(v, c - 1, r), vl = band_uV(v, c - 1, r);
+            if (hl + v.ge < max(hl, vl) + v.go) nib |= kTrHOpen;
+        }
+        int32_t const hu = band_uH(v, c, r - 1), vu = band_uV(v, c, r - 1);
+        if (vu + v.ge < max(hu, vu) + v.go) nib |= kTrVOpen;
+        if (vCur < hCur) nib |= kTrFromH;
+    }
+    else
+    {
+        int32_t const hCur = band_lH(v, c, r), vCur = band_lV(v, c, r);
+        if (r == c - v.dLo + 1) { if (v.lTV[c] < v.lTS[c]) nib |= kTrVOpen; }
+        else
+        {
+            int32_t const hu = band_lH(v, c, r - 1), vu = band_lV(v, c, r - 1);
+            if (vu + v.ge < max(hu, vu) + v.go) nib |= kTrVOpen;
+        }
+        int32_t const hl = band_lH(v, c - 1, r), vl = band_lV(v, c - 1, r);
+        if (hl + v.ge < max(hl, vl) + v.go) nib |= kTrHOpen;
+        if (vCur < hCur) nib |= kTrFromH;
+    }
+    return nib;
+}
+
+// S, V, H of the end cell when it lies outside the band
+__device__ void band_end_values(BandView const & v, int32_t & sE, int32_t & vE, int32_t & hE)
+{
+    int const c = v.la, r = v.lb;
+    if (c - r > v.dHi) { vE = band_uV(v, c, r); hE = band_uH(v, c, r); }
+    else { vE = band_lV(v, c, r); hE = band_lH(v, c, r); }
+    sE = max(vE, hE);
+}
+
+// Traceback + evaluateLines for band mode: the segment walker of traceback_walk over a polymorphic cell fetch.
+// Window = the 8 trace word rows (64 anti-diagonal steps) ending at the walker's step, in shared memory.
+__device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, int32_t hEnd, uint32_t * linesRev,
+                              uint32_t * win, int32_t & gapOut, int lane)
+{
+    int const L = v.L;
+    int32_t const go = v.go, ge = v.ge;
+    int c = v.la, r = v.lb;
+    int n = 0;
+    int32_t gap = 0;
+    int prev = 0, state = 0;
+    int endFix = (vEnd == sEnd) ? 1 : ((hEnd == sEnd) ? 2 : 0);
+    bool first = true;
+    while (c > 0 && r > 0)
+    {
+        // ---- window: trace word rows [rowLo, rowHi], rowHi = (c + r) >> 3 -------------------------------------
+        int const rowHi = (c + r) >> 3, rowLo = max(rowHi - 7, 0);
+        __syncwarp();
+        for (int i = lane; i < 8 * L; i += 32)
+        {
+            int const row = rowLo + i / L;
+            win[i] = row <= rowHi ? (uint32_t)__ldg(v.trace + (size_t)row * L + (i % L)) : 0u;
+        }
+        __syncwarp();
+        // known(ci, ri): the trace decision of that cell can be evaluated now
+        auto fetch = [&](int ci, int ri, bool & known) -> uint32_t
+        {
+            known = false;
+            if (ci < 1 || ri < 1) return 0u;
+            int const dd = ci - ri;
+            if (dd > v.dHi || dd < v.dLo) { known = true; return band_outside_nib(v, ci, ri); }
+            int const s = ci + ri, row = s >> 3;
+            if (row < rowLo) return 0u;
+            known = true;
+            return (win[(row - rowLo) * L + ((dd - v.dLo) >> 1)] >> (4 * (7 - (s & 7)))) & 15u;
+        };
+        for (;;)
+        {
+            if (c <= 0 || r <= 0) break;
+            {
+                int const dd = c - r;
+                if (dd <= v.dHi && dd >= v.dLo && ((c + r) >> 3) < rowLo) break;     // current cell left the window
+            }
+            if (state == 0)
+            {
+                bool known;
+                uint32_t nib = fetch(c - lane, r - lane, known);
+                if (first && lane == 0)
+                {
+                    if (endFix == 1) nib = (nib | kTrGap) & ~kTrFromH;
+                    else if (endFix == 2) nib = nib | kTrGap | kTrFromH;
+                }
+                first = false;
+                unsigned const diagMask = __ballot_sync(kFull, known && !(nib & kTrGap));
+                int const run = (diagMask == kFull) ? 32 : (__ffs(~diagMask) - 1);
+                if (run > 0)
+                {
+                    if (lane < run)
+                        linesRev[n + lane] = ((uint32_t)(c - lane - 1) << 16) | (uint32_t)(r - lane - 1);
+                    n += run; c -= run; r -= run; prev = 0;
+                    continue;
+                }
+                uint32_t const nib0 = __shfl_sync(kFull, nib, 0);
+                state = (nib0 & kTrFromH) ? 2 : 1;
+            }
+            if (state == 1)
+            {
+                bool known;
+                uint32_t const nib = fetch(c, r - lane, known);
+                unsigned const knownMask = __ballot_sync(kFull, known);
+                unsigned const extMask = __ballot_sync(kFull, known && !(nib & kTrVOpen) && (r - lane) != 1);
+                int const m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                bool const closes = m < 32 && ((knownMask >> m) & 1u);
+                int const steps = closes ? m + 1 : m;
+                if (steps > 0)
+                {
+                    gap += ((prev == 1) ? ge : go) + (steps - 1) * ge;
+                    prev = 1;
+                    r -= steps;
+                }
+                state = closes ? 0 : 1;
+                if (steps == 0) break;                      // next cell not in the window: reload
+            }
+            else
+            {
+                bool known;
+                uint32_t const nib = fetch(c - lane, r, known);
+                unsigned const knownMask = __ballot_sync(kFull, known);
+                unsigned const extMask = __ballot_sync(kFull, known && !(nib & kTrHOpen) && (c - lane) != 1);
+                int const m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                bool const closes = m < 32 && ((knownMask >> m) & 1u);
+                int const steps = closes ? m + 1 : m;
+                if (steps > 0)
+                {
+                    gap += ((prev == 2) ? ge : go) + (steps - 1) * ge;
+                    prev = 2;
+                    c -= steps;
+                }
+                state = closes ? 0 : 2;
+                if (steps == 0) break;
+            }
+        }
+    }
     if (r > 0) { gap += ((prev == 1) ? ge : go) + (r - 1) * ge; prev = 1; }
     if (c > 0) { gap += ((prev == 2) ? ge : go) + (c - 1) * ge; prev = 2; }
     gapOut = gap;
@@ -387,12 +570,12 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     // carve the per-warp shared memory
     size_t const candBytes = (size_t)smemCand * 8;
     size_t const lb4 = ((size_t)maxLb * 4 + 15) / 16 * 16;
-    size_t const perWarp = candBytes + 64 + 512 + 2 * lb4 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    size_t const perWarp = candBytes + 64 + 1024 + 2 * lb4 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
     unsigned char * base = smemRaw + (size_t)warpInBlock * perWarp;
     WarpSmem sm;
     sm.cand = (unsigned long long *)base;                     base += candBytes;
     sm.misc = (int32_t *)base;                                base += 64;
-    sm.win = (uint32_t *)base;                                base += 512;
+    sm.win = (uint32_t *)base;                                base += 1024;
     sm.linesRev = (uint32_t *)base;                           base += lb4;
     sm.curE = (int32_t *)base;                                base += lb4;
     sm.lineOfA = (int16_t *)base;                             base += ((size_t)maxLa * 2 + 15) / 16 * 16;
@@ -403,7 +586,28 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
     // ---- 1. traceback + evaluateLines ------------------------------------------------------------
     int32_t gapScore = 0;
-    int const nLines = traceback_walk(d, st, arena, P.go, P.ge, sm.linesRev, sm.win, gapScore, lane);
+    int nLines;
+    if (d.bandL > 0)
+    {
+        BandView bv;
+        bv.la = d.la; bv.lb = d.lb; bv.dLo = d.dLo; bv.dHi = d.dHi; bv.L = d.bandL; bv.go = P.go; bv.ge = P.ge;
+        bv.trace = arena + d.offBTrace;
+        bv.uTH = arena + d.offU; bv.uTS = bv.uTH + (d.lb + 1); bv.uM = bv.uTS + (d.lb + 1);
+        bv.lTV = arena + d.offL; bv.lTS = bv.lTV + (d.la + 1); bv.lM = bv.lTS + (d.la + 1);
+        int32_t sE = st.sEnd, vE = st.vEnd, hE = st.hEnd;
+        int const dEnd = d.la - d.lb;
+        if (dEnd > d.dHi || dEnd < d.dLo)
+        {
+            // the end cell lies in a pure gap region: its values are closed forms too
+            band_end_values(bv, sE, vE, hE);
+            __syncwarp();
+            if (lane == 0) { st.currentUpper = sE; st.sEnd = sE; st.vEnd = vE; st.hEnd = hE; }
+            __syncwarp();
+        }
+        nLines = traceback_band(bv, sE, vE, hE, sm.linesRev, sm.win, gapScore, lane);
+    }
+    else
+        nLines = traceback_walk(d, st, arena, P.go, P.ge, sm.linesRev, sm.win, gapScore, lane);
     if (lane == 0) { sm.misc[0] = 0; sm.misc[1] = 0; sm.misc[2] = 0; sm.misc[11] = 0; }
     for (int a = lane; a < la; a += 32) sm.lineOfA[a] = -1;
     __syncwarp();
@@ -649,7 +853,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
 size_t post_smem_per_warp(int maxLa, int maxLb, int smemCand)
 {
-    return (size_t)smemCand * 8 + 64 + 512 + 2 * (((size_t)maxLb * 4 + 15) / 16 * 16) + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    return (size_t)smemCand * 8 + 64 + 1024 + 2 * (((size_t)maxLb * 4 + 15) / 16 * 16) + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
 }
 
 } // namespace

@@ -145,11 +145,33 @@ edge_filter_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__
     __syncwarp();
     int cnt = 0;
     for (int i = lane; i < nWords; i += 32) cnt += __popc(bits[i]);
+    // diagonal range a - b of the active edges (band geometry of kernels_band.cu)
+    int dmin = INT32_MAX, dmax = INT32_MIN;
+    for (int a = lane; a < la; a += 32)
+    {
+        int bFirst = -1, bLast = -1;
+        for (int w = 0; w < d.bitWords; ++w)
+        {
+            uint32_t const m = bits[(size_t)a * d.bitWords + w];
+            if (m)
+            {
+                if (bFirst < 0) bFirst = (w << 5) + __ffs(m) - 1;
+                bLast = (w << 5) + 31 - __clz(m);
+            }
+        }
+        if (bFirst >= 0) { dmin = min(dmin, a - bLast); dmax = max(dmax, a - bFirst); }
+    }
     #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(kFull, cnt, o);
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        cnt += __shfl_xor_sync(kFull, cnt, o);
+        dmin = min(dmin, __shfl_xor_sync(kFull, dmin, o));
+        dmax = max(dmax, __shfl_xor_sync(kFull, dmax, o));
+    }
     if (lane == 0)
     {
         d.E = cnt;
+        d.dMin = dmin; d.dMax = dmax;
         PairState & st = state[p];
         st.optScore = opt;
         // avgId (src/edge_filter.hpp:157) and sequenceScaleFactor (src/lagrange.hpp:252), no FMA contraction
@@ -289,7 +311,14 @@ setup_count_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__
     }
     if (lane == 0) { ioff[E] = carry; d.D = carry; }
 
-    // 4. geometry of the strip-dense value stream: step flags per lane, stream start per lane
+    // 4. geometry of the value stream
+    if (d.bandL > 0)
+    {
+        // band mode: dense band stream vals[s * bandL + lane]
+        if (lane == 0) d.nVals = d.nSpad * d.bandL;
+        return;
+    }
+    // full-matrix mode: strip-dense stream: step flags per lane, stream start per lane
     int const nFlagWords = (d.nSteps + 31) >> 5;
     uint32_t * __restrict__ flags = (uint32_t *)(arena + d.offFlags) + (size_t)lane * nFlagWords;
     for (int w = 0; w < nFlagWords; ++w) flags[w] = 0u;
@@ -362,9 +391,26 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
             rev[x] = r;
             if (r < 0) state[p].error = 3;
         }
-    // 3. value stream + permutation: lane k walks its own stream in step order
+    // 3. value stream + permutation
     int32_t * __restrict__ vals = arena + d.offVals;
     int32_t * __restrict__ perm = arena + d.offPerm;
+    if (d.bandL > 0)
+    {
+        // band mode: cell (a, b) = matrix cell (c, r) = (a + 1, b + 1) sits at step s = c + r on diagonal a - b
+        __syncwarp();
+        for (int i = lane; i < d.nVals; i += 32) vals[i] = kDpNeg;
+        __syncwarp();
+        for (int e = lane; e < E; e += 32)
+        {
+            int const ab = cell[e];
+            int const a = ab >> 16, b = ab & 0xffff;
+            int const idx = (a + b + 2) * d.bandL + ((a - b - d.dLo) >> 1);
+            vals[idx] = pv[e];
+            perm[e] = idx;
+        }
+    }
+    else
+    {
     int ptr = arena[d.offLanePtr + lane];
     int const lo = lane * R, len = min(R, max(0, lb - lo));
     for (int a = 0; a < la; ++a)
@@ -378,6 +424,7 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
             else vals[ptr + j] = kDpNeg;
         }
         ptr += R;
+    }
     }
     // 4. solver state (src/subgradient_solver.hpp:86-100, simd :153,387-393)
     if (lane == 0)

@@ -91,6 +91,8 @@ struct lara_ctx
     std::deque<Device> devs;                // deque: Device holds a mutex and is not movable
     int nWorkers = 3;                       // concurrent batches per device (env LARA_B200_WORKERS)
     size_t batchPairsDefault = 8192;        // pairs per batch (env LARA_B200_BATCH)
+    bool bandMode = true;                   // band DP kernels where the active edges allow it (env LARA_B200_BAND=0: off)
+    int bandMargin = 1;                     // diagonals added on both sides of the active range (env LARA_B200_MARGIN)
     // host copy of the inputs (for pair orientation and batch sizing)
     int32_t nSeq = 0;
     std::vector<int64_t> seqOff, bpOff;
@@ -166,6 +168,27 @@ double ev_ms(cudaEvent_t a, cudaEvent_t b)
     return (double)ms;
 }
 
+// Band geometry of one pair from the diagonal range of its active edges (kernels_band.cu): dLo even,
+// dLo <= 0 <= dHi, 2 * bandL diagonals.  bandL = 0 selects the full-matrix kernel (band wider than 64
+// diagonals, or gap costs outside the band kernel's precondition go < ge).
+void choose_band(lara_ctx const & ctx, PairDesc & d)
+{
+    d.bandL = 0; d.dLo = 0; d.dHi = -1; d.nSpad = 0;
+    if (!ctx.bandMode || !(ctx.dp.go < ctx.dp.ge)) return;
+    int lo = 0, hi = 0;
+    if (d.E > 0 && d.dMin <= d.dMax)
+    {
+        lo = std::min(d.dMin - ctx.bandMargin, 0);
+        hi = std::max(d.dMax + ctx.bandMargin, 0);
+    }
+    if (lo & 1) lo -= 1;
+    int const need = hi - lo + 1;
+    int const L = need <= 32 ? 16 : (need <= 64 ? 32 : 0);
+    if (L == 0) return;
+    d.bandL = L; d.dLo = lo; d.dHi = lo + 2 * L - 1;
+    d.nSpad = (d.la + d.lb + 3 + 7) & ~7;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // One batch: pairs [begin, end) of dv.pairs (already length sorted).
 // ---------------------------------------------------------------------------------------------------
@@ -234,7 +257,14 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     wk.stats.kernel_launches += 1;
     // ---- stage B layout: per-edge arrays ---------------------------------------------------------------
     int64_t sizeB = 0;
-    for (int i = 0; i < n; ++i) sizeB += 4 * align4(std::max(desc[(size_t)i].E, 1)) + align4(desc[(size_t)i].E + 1);
+    for (int i = 0; i < n; ++i)
+    {
+        PairDesc & d = desc[(size_t)i];
+        choose_band(ctx, d);
+        sizeB += 4 * align4(std::max(d.E, 1)) + align4(d.E + 1);
+        if (d.bandL > 0)
+            sizeB += align4((int64_t)d.nSpad / 8 * d.bandL) + align4(3ll * (d.lb + 1)) + align4(3ll * (d.la + 1));
+    }
     Region rB;
     CK(cudaMallocAsync((void **)&rB.ptr, (size_t)sizeB * 4, s));
     rB.size = sizeB; rB.baseDelta = rB.ptr - arena;
@@ -243,6 +273,13 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         PairDesc & d = desc[(size_t)i];
         d.offCell = rB.take(d.E); d.offSeqScore = rB.take(d.E); d.offPv = rB.take(d.E); d.offPerm = rB.take(d.E);
         d.offIoff = rB.take(d.E + 1);
+        if (d.bandL > 0)
+        {
+            d.offBTrace = rB.take((int64_t)d.nSpad / 8 * d.bandL);
+            d.offU = rB.take(3ll * (d.lb + 1));
+            d.offL = rB.take(3ll * (d.la + 1));
+            ++wk.stats.reserved[1];                     // pairs solved by the band kernels
+        }
     }
     CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
     // ---- stage 2: counts -> D, nVals -----------------------------------------------------------------------
@@ -270,8 +307,10 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     CK(cudaEventRecord(evS1, s));
 
     // ---- rows-per-lane classes for the DP launches -------------------------------------------------------------
+    // class key: rows per lane R (full-matrix kernel) or -bandL (band kernel)
     std::map<int, std::vector<int32_t>> classes;
-    for (int i = 0; i < n; ++i) classes[desc[(size_t)i].R].push_back(i);
+    for (int i = 0; i < n; ++i)
+        classes[desc[(size_t)i].bandL > 0 ? -desc[(size_t)i].bandL : desc[(size_t)i].R].push_back(i);
     std::vector<int32_t> idxAll;
     std::vector<std::tuple<int, int, int>> cls;        // R, offset, count
     for (auto & kv : classes)
@@ -305,8 +344,12 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it], s));
         for (auto const & c : cls)
         {
-            CK(launch_gotoh_fill(std::get<0>(c), std::get<2>(c), dIdx + std::get<1>(c), dDesc, dState, arena, dv.negBuf,
-                                 dp.go, dp.ge, s));
+            if (std::get<0>(c) < 0)
+                CK(launch_gotoh_band(-std::get<0>(c), std::get<2>(c), dIdx + std::get<1>(c), dDesc, dState, arena,
+                                     dp.go, dp.ge, s));
+            else
+                CK(launch_gotoh_fill(std::get<0>(c), std::get<2>(c), dIdx + std::get<1>(c), dDesc, dState, arena, dv.negBuf,
+                                     dp.go, dp.ge, s));
             wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
         }
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 1], s));
@@ -441,6 +484,7 @@ void run_device(lara_ctx & ctx, Device & dv)
             dv.stats.n_active_edges += wk.stats.n_active_edges; dv.stats.n_interactions += wk.stats.n_interactions;
         }
         dv.stats.reserved[0] = nW;
+        for (int w = 0; w < nW; ++w) dv.stats.reserved[1] += dv.workers[(size_t)w].stats.reserved[1];
     }
     catch (std::exception const & e)
     {
@@ -502,6 +546,8 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
         ids.assign(device_ids, device_ids + n_devices);
     lara_ctx * ctx = new lara_ctx();
     if (char const * e = std::getenv("LARA_B200_WORKERS")) ctx->nWorkers = std::max(1, std::min(8, std::atoi(e)));
+    if (char const * e = std::getenv("LARA_B200_BAND")) ctx->bandMode = std::atoi(e) != 0;
+    if (char const * e = std::getenv("LARA_B200_MARGIN")) ctx->bandMargin = std::max(0, std::min(16, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
     ctx->P = *params;
     ctx->dp = make_dev_params(*params);
@@ -732,6 +778,8 @@ int lara_gpu_run_prepared(lara_ctx * ctx)
         agg.kernel_launches += dv.stats.kernel_launches; agg.filter_cells += dv.stats.filter_cells;
         agg.n_pairs += dv.stats.n_pairs; agg.sum_iterations += dv.stats.sum_iterations;
         agg.n_active_edges += dv.stats.n_active_edges; agg.n_interactions += dv.stats.n_interactions;
+        agg.reserved[0] = std::max(agg.reserved[0], dv.stats.reserved[0]);     // concurrent workers per device
+        agg.reserved[1] += dv.stats.reserved[1];                               // pairs solved by the band kernels
     }
     agg.ms_total = ms;
     ctx->stats = agg;
@@ -915,6 +963,92 @@ int lara_gpu_gotoh_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32
             }
         }
         cudaFree(dPssm); cudaFree(dState); cudaFree(dDesc); cudaFree(arena);
+    }
+    catch (std::exception const & ex)
+    {
+        return set_err(ctx, LARA_E_CUDA, ex.what());
+    }
+    return LARA_OK;
+}
+
+int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32_t lenB, int32_t const * pssm,
+                              int32_t d_lo, int32_t lanes, int32_t gap_open, int32_t gap_extend, int32_t * score,
+                              int32_t * n_lines, int32_t * lines_a, int32_t * lines_b, int32_t * gap_score)
+{
+    if (!ctx || !pssm || n_problems < 1 || lenA < 1 || lenB < 1) return set_err(ctx, LARA_E_INVALID, "bad argument");
+    if ((lanes != 16 && lanes != 32) || (d_lo & 1) || d_lo > 0 || d_lo + 2 * lanes - 1 < 0)
+        return set_err(ctx, LARA_E_INVALID, "band: lanes must be 16 or 32, d_lo even and d_lo <= 0 <= d_lo + 2 * lanes - 1");
+    if (!(gap_open < gap_extend)) return set_err(ctx, LARA_E_UNSUPPORTED, "band kernel needs gap_open < gap_extend");
+    Device & dv = ctx->devs[0];
+    cudaStream_t const s = dv.stream;
+    int const n = n_problems, L = lanes, dHi = d_lo + 2 * L - 1;
+    try
+    {
+        CK(cudaSetDevice(dv.id));
+        std::vector<PairDesc> desc((size_t)n);
+        Region rg;
+        int const nSpad = (lenA + lenB + 3 + 7) & ~7;
+        for (int pass = 0; pass < 2; ++pass)
+        {
+            rg.used = 0;
+            for (int i = 0; i < n; ++i)
+            {
+                PairDesc & d = desc[(size_t)i];
+                std::memset(&d, 0, sizeof(d));
+                d.la = lenA; d.lb = lenB; d.bandL = L; d.dLo = d_lo; d.dHi = dHi; d.nSpad = nSpad;
+                d.nVals = nSpad * L;
+                d.offVals = rg.take(d.nVals);
+                d.offBTrace = rg.take((int64_t)nSpad / 8 * L);
+                d.offU = rg.take(3ll * (lenB + 1));
+                d.offL = rg.take(3ll * (lenA + 1));
+                d.offLines = rg.take(lenB);
+            }
+            if (pass == 0) CK(cudaMalloc((void **)&rg.ptr, (size_t)rg.used * 4));
+        }
+        // dense band stream on the host: cell (a, b) -> step a + b + 2, lane (a - b - d_lo) >> 1
+        std::vector<int32_t> host((size_t)rg.used, kDpNeg);
+        for (int i = 0; i < n; ++i)
+            for (int a = 0; a < lenA; ++a)
+                for (int b = 0; b < lenB; ++b)
+                {
+                    int32_t const v = pssm[((size_t)i * lenA + a) * lenB + b];
+                    if (v <= kDpNeg) continue;
+                    if (a - b < d_lo || a - b > dHi)
+                    {
+                        cudaFree(rg.ptr);
+                        return set_err(ctx, LARA_E_INVALID, "band: active cell outside the band");
+                    }
+                    host[(size_t)desc[(size_t)i].offVals + (size_t)(a + b + 2) * L + ((a - b - d_lo) >> 1)] = v;
+                }
+        int32_t * arena = rg.ptr;
+        PairDesc * dDesc; PairState * dState;
+        CK(cudaMalloc((void **)&dDesc, sizeof(PairDesc) * (size_t)n));
+        CK(cudaMalloc((void **)&dState, sizeof(PairState) * (size_t)n));
+        CK(cudaMemcpyAsync(arena, host.data(), host.size() * 4, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
+        CK(cudaMemsetAsync(dState, 0, sizeof(PairState) * (size_t)n, s));
+        CK(launch_gotoh_band(L, n, nullptr, dDesc, dState, arena, gap_open, gap_extend, s));
+        CK(launch_traceback_only(n, dDesc, dState, arena, gap_open, gap_extend, lenA, lenB, s));
+        std::vector<PairState> hs((size_t)n);
+        CK(cudaMemcpyAsync(hs.data(), dState, sizeof(PairState) * (size_t)n, cudaMemcpyDeviceToHost, s));
+        std::vector<int32_t> lines((size_t)n * lenB);
+        for (int i = 0; i < n; ++i)
+            CK(cudaMemcpyAsync(lines.data() + (size_t)i * lenB, arena + desc[(size_t)i].offLines, sizeof(int32_t) * (size_t)lenB,
+                               cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        for (int i = 0; i < n; ++i)
+        {
+            if (score) score[i] = hs[(size_t)i].currentUpper;
+            if (n_lines) n_lines[i] = hs[(size_t)i].nLines;
+            if (gap_score) gap_score[i] = hs[(size_t)i].gapScore;
+            for (int k = 0; k < hs[(size_t)i].nLines; ++k)
+            {
+                uint32_t const v = (uint32_t)lines[(size_t)i * lenB + k];
+                if (lines_a) lines_a[(size_t)i * lenB + k] = (int32_t)(v >> 16);
+                if (lines_b) lines_b[(size_t)i * lenB + k] = (int32_t)(v & 0xffffu);
+            }
+        }
+        cudaFree(dState); cudaFree(dDesc); cudaFree(arena);
     }
     catch (std::exception const & ex)
     {

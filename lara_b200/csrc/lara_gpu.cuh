@@ -23,6 +23,8 @@ constexpr int32_t kDpNeg = INT32_MIN / 2;
 constexpr int32_t kPssmInit = -1431655764;
 // src/data_types.hpp:77
 constexpr int32_t kInf = LARA_INFINITY;
+// band DP: value of cells that do not exist (yet); never wins, never overflows when a gap cost or kDpNeg is added
+constexpr int32_t kBandNeg = -(1 << 29);
 
 constexpr int kWarp = 32;
 // Largest rows-per-lane the single-pass DP kernel is instantiated for: lenB <= 32 * kMaxR.
@@ -75,6 +77,14 @@ struct PairDesc
     int64_t offBest;            // best lines     (a << 16) | b | matched << 31  [lb]
     int64_t offCand;            // global candidate buffer for the matching sort, 2 words each [2 * kCap] (8-byte aligned)
     int64_t offScratch;         // set-up scratch: forward prefix scores [la * lb]
+    // ---- band mode (kernels_band.cu): the DP runs only over the diagonals dLo <= c - r <= dHi ------------
+    int32_t dMin, dMax;         // diagonal range (a - b) of the active edges (edge filter); dMin > dMax: none
+    int32_t bandL;              // lanes per pair of the band DP: 16 or 32 (band = 2 * bandL diagonals); 0 = full matrix
+    int32_t dLo, dHi;           // band (dLo even, dLo <= 0 <= dHi, dHi = dLo + 2 * bandL - 1)
+    int32_t nSpad;              // anti-diagonal steps of the band DP, multiple of 8 (>= la + lb + 3)
+    int64_t offBTrace;          // band trace: word [(s >> 3) * bandL + lane], nibble 7 - (s & 7)   [nSpad / 8 * bandL]
+    int64_t offU;               // region U (c - r > dHi): TH[lb + 1], TS[lb + 1], M[lb + 1]
+    int64_t offL;               // region L (c - r < dLo): TV[la + 1], TS[la + 1], M[la + 1]
 };
 
 // Mutable per-pair solver state (BoundInfo + SubgradientSolver fields, src/subgradient_solver.hpp:64-108).
@@ -129,6 +139,9 @@ struct PairOutHdr
 // DP fill over the pairs listed in pairIdx[0..n) that all have the same R.
 cudaError_t launch_gotoh_fill(int R, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t const * negBuf, int32_t go, int32_t ge, cudaStream_t stream);
+// band DP fill (kernels_band.cu) over the pairs listed in pairIdx[0..n) that all have bandL == L (16 or 32)
+cudaError_t launch_gotoh_band(int L, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
+                              int32_t * arena, int32_t go, int32_t ge, cudaStream_t stream);
 // traceback + valid_solution + matching + bounds + update for all n pairs of the batch
 cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                 DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
