@@ -286,6 +286,10 @@ def main():
         cells += st.dp_cells
         launches += st.kernel_launches
         dp_launches += st.dp_launches
+        log("step: %.1f ms device, dp %.1f post %.1f setup %.1f (summed over %d concurrent workers), band pairs %d (32-diag %d) of %d, "
+            "mean iterations %.1f, E/pair %.0f, D/pair %.0f"
+            % (st.ms_device, st.ms_dp, st.ms_bounds, st.ms_setup, st.reserved[0], st.reserved[1], st.reserved[2], st.n_pairs,
+               st.sum_iterations / max(st.n_pairs, 1), st.n_active_edges / max(st.n_pairs, 1), st.n_interactions / max(st.n_pairs, 1)))
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - wall0)
     clocks = sampler.stop() if rank == 0 else None

@@ -184,12 +184,15 @@ int lara_gpu_gotoh_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32
 
 /*
  * The same alignment computed by the BAND kernels (lara_b200/csrc/kernels_band.cu): only the diagonals
- * d_lo <= a - b <= d_lo + 2 * lanes - 1 are filled (lanes = 16 or 32, d_lo even and <= 0), the rest of the matrix is
- * covered by closed forms.  Every active cell (pssm > -2^30) must lie inside the band; the result is then
- * identical to lara_gpu_gotoh_batch.  Needs gap_open < gap_extend.
+ * d_lo <= a - b <= d_lo + band_width - 1 are filled (d_lo <= 0 <= d_lo + band_width - 1), the rest of the matrix is
+ * covered by closed forms.  `lanes` threads work on one problem, each on two blocks of band_width / (2 * lanes)
+ * diagonals; supported: blocks of 16 diagonals with 1, 2, 4, 8, 16 or 32 lanes (band_width 32 .. 1024) and blocks of
+ * 4 diagonals with 4, 8, 16 or 32 lanes (band_width 32 .. 256).  Every active cell (pssm > -2^30) must lie inside the
+ * band; the result is then identical to lara_gpu_gotoh_batch.  Needs gap_open < gap_extend.
  */
 int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32_t lenB,
-                              int32_t const * pssm, int32_t d_lo, int32_t lanes, int32_t gap_open, int32_t gap_extend,
+                              int32_t const * pssm, int32_t d_lo, int32_t band_width, int32_t lanes,
+                              int32_t gap_open, int32_t gap_extend,
                               int32_t * score, int32_t * n_lines, int32_t * lines_a, int32_t * lines_b,
                               int32_t * gap_score);
 

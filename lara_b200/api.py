@@ -279,8 +279,9 @@ class Context:
                                                    gap.ctypes.data))
         return score, nl, la_, lb_, gap
 
-    def gotoh_band_batch(self, pssm, d_lo, lanes, gap_open, gap_extend):
-        """Band kernels on the same problem as gotoh_batch; all active cells must lie inside the band."""
+    def gotoh_band_batch(self, pssm, d_lo, band_width, lanes, gap_open, gap_extend):
+        """Band kernels on the same problem as gotoh_batch; all active cells must lie inside the band
+        d_lo <= a - b < d_lo + band_width; `lanes` threads per problem."""
         pssm = np.ascontiguousarray(pssm, dtype=np.int32)
         n, la, lb = pssm.shape
         score = np.zeros(n, np.int32)
@@ -288,7 +289,7 @@ class Context:
         la_ = np.zeros((n, lb), np.int32)
         lb_ = np.zeros((n, lb), np.int32)
         gap = np.zeros(n, np.int32)
-        self._check(self._lib.lara_gpu_gotoh_band_batch(self._h, n, la, lb, pssm.ctypes.data, d_lo, lanes, gap_open,
+        self._check(self._lib.lara_gpu_gotoh_band_batch(self._h, n, la, lb, pssm.ctypes.data, d_lo, band_width, lanes, gap_open,
                                                         gap_extend, score.ctypes.data, nl.ctypes.data, la_.ctypes.data,
                                                         lb_.ctypes.data, gap.ctypes.data))
         return score, nl, la_, lb_, gap

@@ -16,16 +16,29 @@
 //   region L (c - r < dLo): the same with rows/columns and H/V exchanged.
 //
 // The lane that owns the top (bottom) diagonal keeps the running maximum in a register, feeds the inflow from U
-// (L) into its cell and records TH/TS/M per row (TV/TS/M per column) so that a traceback that leaves the band can
-// be continued exactly (kernels_post.cu).  Requires go < ge (opening dearer than extending).
+// (L) into its cells and records TH/TS/M per row (TV/TS/M per column) so that a traceback that leaves the band
+// can be continued exactly (kernels_post.cu).  Requires go < ge (opening dearer than extending).
 //
-// Mapping: anti-diagonal wavefront.  A pair uses L lanes (16 or 32; 32 / L pairs per warp); lane l owns the
-// two diagonals dA = dLo + 2l and dB = dA + 1.  Step s handles the cells with c + r = s: even steps the A
-// diagonals, odd steps the B diagonals (dLo is even), so every lane updates exactly one cell per step:
-//     A cell: left neighbour = B cell of lane l-1 (shfl_up), upper neighbour = own B cell, diagonal = own A cell
-//     B cell: left neighbour = own A cell, upper neighbour = A cell of lane l+1 (shfl_down), diagonal = own B
-// Position specific scores come from a dense band stream vals[s * L + l] (coalesced), four decision bits per
-// cell go to trace[(s >> 3) * L + l] (one word per lane and 8 steps, coalesced).
+// Mapping: a band of W = 2 G Q diagonals is cut into 2 G blocks of Q neighbouring diagonals; lane g of the G
+// lanes of a pair owns blocks A = 2g and B = 2g + 1, so 32 / G pairs share a warp (G = 1: one THREAD per pair, the
+// inter-sequence parallelism of the reference's SIMD kernel; larger G when a batch has too few pairs to fill
+// the machine or the band is wide).  Block b works on row r in time step 2 r + b: in loop iteration i lane g
+// computes row r = i - g + 1 of block A and then of block B, each a run of Q cells of one matrix row:
+//     left neighbour of the run   = last cell of the previous block in the same row
+//                                   (A: block B of lane g-1, one iteration ago, by shfl_up;   B: own block A)
+//     upper neighbours            = the cells one diagonal higher in row r - 1: own registers, and for the last
+//                                   cell the first diagonal of the next block (A: own block B;  B: block A of lane
+//                                   g+1 from this iteration, by shfl_down)
+//     diagonal neighbour          = previous cell of the same diagonal (same register)
+// so a lane keeps S and V of the latest cell of each of its 2 Q diagonals in registers and two shuffles serve Q
+// cells.  The horizontal chain along a run is shortened to IADD + VIMNMX per cell: with go < ge,
+//     H(c,r) = max(H(c-1,r) + ge, S(c-1,r) + go) = max(H(c-1,r) + ge, max(D(c-1,r), V(c-1,r)) + go)
+// and the "H opened" decision bit (first operand wins ties) is unchanged by dropping H(c-1,r) from the second
+// operand, because H + ge > H + go.
+//
+// Memory: position specific scores come from a dense band array vals[row][diagonal], stored in 16-byte chunks of 4
+// diagonals and interleaved over the pairs of a warp ([row][chunk][pair slot]) so that a warp-wide 128-bit load is
+// contiguous; four decision bits per cell go to trace units of Q nibbles ([row][block][pair slot]).
 #include "lara_gpu.cuh"
 
 namespace lara
@@ -36,152 +49,237 @@ namespace
 
 constexpr unsigned kFull = 0xffffffffu;
 
-// One SeqAn _maxScore step (see kernels_dp.cu): max(a, b) with a winning ties; decision bit = "b won".
-__device__ __forceinline__ int32_t max_push(int32_t a, int32_t b, uint32_t & tw)
+template <int Q> struct TraceUnit;
+template <> struct TraceUnit<4>  { using type = uint16_t; };
+template <> struct TraceUnit<8>  { using type = uint32_t; };
+template <> struct TraceUnit<16> { using type = uint2; };
+
+template <int Q>
+__device__ __forceinline__ void store_unit(void * base, size_t unitIdx, uint32_t const (&tw)[(Q + 7) / 8])
 {
-    tw = __funnelshift_l((uint32_t)(a - b), tw, 1);
-    return max(a, b);
+    if constexpr (Q == 4) reinterpret_cast<uint16_t *>(base)[unitIdx] = (uint16_t)(tw[0] >> 16);
+    else if constexpr (Q == 8) reinterpret_cast<uint32_t *>(base)[unitIdx] = tw[0];
+    else reinterpret_cast<uint2 *>(base)[unitIdx] = make_uint2(tw[0], tw[1]);
 }
 
-template <int L>
+// One run of Q cells of row r on the diagonals of one block.  S[j], V[j]: latest cell of diagonal j (row r - 1 on
+// entry, row r on exit).  (hL, sL): H and S of the left neighbour of the run; (sU, vU): S and V of the upper
+// neighbour of the run's last cell.  Returns H of the run's last cell.  tw: Q decision nibbles, cell j in
+// word j / 8 at bits 4 (j % 8) (Q = 4: in the upper half word).
+// kLast: additionally captures S, V, H of cell jEnd (the end cell of the matrix, for SeqAn's _correctTraceValue).
+template <int Q, bool kLast>
+__device__ __forceinline__ int32_t band_run(int32_t (&S)[Q], int32_t (&V)[Q], int32_t const (&sub)[Q], int32_t hL, int32_t sL,
+                                            int32_t sU, int32_t vU, int32_t go, int32_t ge, uint32_t (&tw)[(Q + 7) / 8],
+                                            int jEnd, int32_t & sE, int32_t & vE, int32_t & hE)
+{
+    int32_t h = hL, m = sL + go;
+    #pragma unroll
+    for (int j = 0; j < Q; ++j)
+    {
+        int32_t const us = (j + 1 < Q) ? S[j + 1] : sU;
+        int32_t const uv = (j + 1 < Q) ? V[j + 1] : vU;
+        int32_t const dd = S[j] + sub[j];
+        int32_t const ve = uv + ge, vo = us + go;
+        int32_t const v = max(ve, vo);
+        int32_t const he = h + ge;
+        int32_t const hn = max(he, m);
+        int32_t const gg = max(v, hn);
+        int32_t const s = max(dd, gg);
+        uint32_t n = (uint32_t)(he - m) >> 31;                          // bit 3: H opened   (extension wins ties)
+        n = __funnelshift_l((uint32_t)(ve - vo), n, 1);                 // bit 2: V opened   (extension wins ties)
+        n = __funnelshift_l((uint32_t)(v - hn), n, 1);                  // bit 1: gap from H (vertical wins ties)
+        n = __funnelshift_l((uint32_t)(dd - gg), n, 1);                 // bit 0: S from gap (diagonal wins ties)
+        tw[j >> 3] = __funnelshift_r(tw[j >> 3], n, 4);
+        m = max(dd, v) + go;
+        h = hn;
+        S[j] = s;
+        V[j] = v;
+        if (kLast && j == jEnd) { sE = s; vE = v; hE = hn; }
+    }
+    return h;
+}
+
+template <int G, int Q>
 __global__ void __launch_bounds__(128)
-gotoh_band_kernel(int n, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc,
+gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc,
                   PairState * __restrict__ state, int32_t * __restrict__ arena, int32_t go, int32_t ge)
 {
-    constexpr int PPW = 32 / L;                                 // pairs per warp
+    constexpr int PPW = 32 / G;                                 // pairs per warp
+    constexpr int W = 2 * G * Q;                                // diagonals of the band
+    constexpr int NCH = W / 4;                                  // 16-byte value chunks per row
+    constexpr int NU = 2 * G;                                   // trace units per row
+    constexpr int CQ = Q / 4;                                   // value chunks per block
+    constexpr int TW = (Q + 7) / 8;
     int const warp = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
     int const lane = threadIdx.x & 31;
-    int const l = lane % L;                                     // lane inside the pair
-    int const slot = warp * PPW + lane / L;
-    if (warp * PPW >= n)
+    if (warp * PPW >= nSlots)
         return;
-    bool live = slot < n;
-    int p = 0;
-    if (live)
-    {
-        p = pairIdx ? pairIdx[slot] : slot;
-        live = state[p].done == 0;
-    }
-    PairDesc const & d = desc[p];
-    // a dead sub-group runs along with la = lb = -2: no cell is ever valid, nothing is stored
-    int const la = live ? d.la : -2, lb = live ? d.lb : -2;
+    int const q = lane / G, g = lane % G;
+    int const slot = warp * PPW + q;
+    int p = slot < nSlots ? pairIdx[slot] : -1;
+    if (p >= 0 && state[p].done)
+        p = -1;
+    bool const live = p >= 0;
+    PairDesc const & d = desc[live ? p : 0];
+    int const la = live ? d.la : -1, lb = live ? d.lb : -1;
     int const dLo = live ? d.dLo : 0;
-    int const dHi = dLo + 2 * L - 1;
-    int nSpad = live ? d.nSpad : 0;
+    int lbMax = lb;
     #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) nSpad = max(nSpad, __shfl_xor_sync(kFull, nSpad, o));
-    int32_t const * __restrict__ vals = arena + d.offVals + l;
-    int32_t * __restrict__ trace = arena + d.offBTrace + l;
+    for (int o = 16; o > 0; o >>= 1) lbMax = max(lbMax, __shfl_xor_sync(kFull, lbMax, o));
+    if (lbMax < 1)
+        return;
+
+    int4 const * __restrict__ vals = reinterpret_cast<int4 const *>(arena + d.offBVals) + q;
+    void * const trace = arena + d.offBTrace;
     int32_t * __restrict__ uTH = arena + d.offU, * uTS = uTH + (lb + 1), * uM = uTS + (lb + 1);
     int32_t * __restrict__ lTV = arena + d.offL, * lTS = lTV + (la + 1), * lM = lTS + (la + 1);
 
-    int const dA = dLo + 2 * l;
-    int32_t SA = kBandNeg, HA = kBandNeg, VA = kBandNeg;       // latest cell on diagonal dA
-    int32_t SB = kBandNeg, HB = kBandNeg, VB = kBandNeg;       // latest cell on diagonal dB = dA + 1
-    int32_t runU = kDpNeg, runL = kDpNeg;                       // running maxima M(r) (lane L-1) / M'(c) (lane 0)
-    uint32_t tw = 0;
-    int32_t subA = live ? __ldg(vals) : kDpNeg;                 // s = 0
-    int32_t subB = live ? __ldg(vals + L) : kDpNeg;             // s = 1
+    // end cell (la, lb): block and diagonal inside the block, if it lies in the band
+    int const idxEnd = la - lb - dLo;
+    int const bEnd = (live && idxEnd >= 0 && idxEnd < W) ? idxEnd / Q : -1;
+    int const jEnd = idxEnd - bEnd * Q;
 
-    for (int s = 0; s < nSpad; s += 2)
+    // ---- row 0 (dp_formula_affine.h:245-281): S(c,0) = H(c,0) = go + (c-1) ge, V = -inf; origin S = 0 -----------
+    int32_t SA[Q], VA[Q], SB[Q], VB[Q];
+    int const cA0 = dLo + 2 * g * Q, cB0 = cA0 + Q;               // column of the blocks' first diagonal in row 0
+    #pragma unroll
+    for (int j = 0; j < Q; ++j)
     {
-        // prefetch the scores of the next double step
-        int32_t nextA = kDpNeg, nextB = kDpNeg;
-        if (live && s + 2 < d.nSpad)
+        int const ca = cA0 + j, cb = cB0 + j;
+        SA[j] = ca > 0 ? go + (ca - 1) * ge : (ca == 0 ? 0 : kBandNeg);
+        SB[j] = cb > 0 ? go + (cb - 1) * ge : (cb == 0 ? 0 : kBandNeg);
+        VA[j] = kBandNeg;
+        VB[j] = kBandNeg;
+    }
+    int32_t HA = (cA0 + Q - 1 > 0) ? SA[Q - 1] : kBandNeg;        // H of the last cell of the block's latest run
+    int32_t HB = (cB0 + Q - 1 > 0) ? SB[Q - 1] : kBandNeg;
+    int32_t runU = kDpNeg, runL = kDpNeg;                         // running maxima M(r) (lane G-1) / M'(c) (lane 0)
+    int32_t sE = 0, vE = 0, hE = 0;
+
+    // scores of one run: CQ 16-byte chunks (software pipelined: block B's are fetched while block A computes,
+    // the next row's block A while block B computes)
+    auto load_run = [&](int32_t (&sub)[Q], int row, int block)
+    {
+        int4 const * __restrict__ src = vals + ((size_t)row * NCH + (size_t)block * CQ) * PPW;
+        #pragma unroll
+        for (int k = 0; k < CQ; ++k)
         {
-            nextA = __ldg(vals + (size_t)(s + 2) * L);
-            nextB = __ldg(vals + (size_t)(s + 3) * L);
+            int4 const x = __ldg(src + (size_t)k * PPW);
+            sub[4 * k] = x.x; sub[4 * k + 1] = x.y; sub[4 * k + 2] = x.z; sub[4 * k + 3] = x.w;
         }
-        // ------------------------------ A step: cells with c + r = s on the even diagonals -------------------
+    };
+    int32_t subA[Q], subB[Q];
+    #pragma unroll
+    for (int j = 0; j < Q; ++j) { subA[j] = kDpNeg; subB[j] = kDpNeg; }
+    if (1 - g >= 1 && 1 - g <= lb) load_run(subA, 1 - g, 2 * g);
+
+    int const nIter = lbMax + G;
+    for (int i = 0; i < nIter; ++i)
+    {
+        int const r = i - g + 1;
+        bool const rowValid = r >= 1 && r <= lb;
+        if (rowValid) load_run(subB, r, 2 * g + 1);
+        // ------------------------------ block A ----------------------------------------------------------------
         {
-            int const c = (s + dA) >> 1, r = (s - dA) >> 1;
-            bool const valid = (c | r) >= 0 && c <= la && r <= lb;
-            int32_t Hl = __shfl_up_sync(kFull, HB, 1, L);
-            int32_t Sl = __shfl_up_sync(kFull, SB, 1, L);
-            if (l == 0)
+            int32_t hL = __shfl_up_sync(kFull, HB, 1, G);
+            int32_t sL = __shfl_up_sync(kFull, SB[Q - 1], 1, G);
+            if (g == 0)
             {
-                // left neighbour (c-1, r) lies in region L, directly below the boundary cell (c-1, r-1) = (SA, VA)
-                Hl = kBandNeg; Sl = kBandNeg;
-                if (c >= 1 && c - 1 <= la && r - 1 <= lb)
+                // the left neighbour (c-1, r) of the run lies in region L, directly below the boundary cell
+                // (c-1, r-1) = latest cell of diagonal dLo = (SA[0], VA[0])
+                int const c = r + dLo;
+                hL = kBandNeg; sL = kBandNeg;
+                if (rowValid && c >= 1 && c - 1 <= la)
                 {
-                    int32_t const tv = VA + ge, ts = SA + go;
-                    int32_t const Vl = max(tv, ts);                              // first L cell of column c-1
-                    Hl = (c - 1 >= 1) ? (c + r - 2) * ge + go + runL : kBandNeg;
-                    Sl = max(Vl, Hl);
+                    int32_t const tv = VA[0] + ge, ts = SA[0] + go;
+                    int32_t const vl = max(tv, ts);                              // first L cell of column c-1
+                    hL = (c - 1 >= 1) ? (c + r - 2) * ge + go + runL : kBandNeg;
+                    sL = max(vl, hL);
                     lTV[c - 1] = tv - r * ge; lTS[c - 1] = ts - r * ge; lM[c - 1] = runL;
-                    runL = max(runL, Vl - r * ge - (c - 1) * ge);
+                    runL = max(runL, vl - r * ge - (c - 1) * ge);
                 }
             }
-            int32_t const dd = SA + subA;
-            int32_t const h = max_push(Hl + ge, Sl + go, tw);     // bit 3: H opened   (extension wins ties)
-            int32_t const v = max_push(VB + ge, SB + go, tw);     // bit 2: V opened   (extension wins ties)
-            int32_t const g = max_push(v, h, tw);                 // bit 1: gap from H (vertical wins ties)
-            int32_t const sc = max_push(dd, g, tw);               // bit 0: S from gap (diagonal wins ties)
-            if (valid) { SA = sc; HA = h; VA = v; }
-            if (s == 0 && dA == 0 && live) { SA = 0; HA = kBandNeg; VA = kBandNeg; }     // origin
-            if (valid && c == la && r == lb)
+            if (rowValid)
             {
-                PairState & st = state[p];
-                st.currentUpper = sc; st.sEnd = sc; st.vEnd = v; st.hEnd = h;
+                uint32_t tw[TW];
+                #pragma unroll
+                for (int k = 0; k < TW; ++k) tw[k] = 0u;
+                if (r == lb && bEnd == 2 * g)
+                    HA = band_run<Q, true>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, tw, jEnd, sE, vE, hE);
+                else
+                    HA = band_run<Q, false>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, tw, 0, sE, vE, hE);
+                store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g)) * PPW + q, tw);
             }
         }
-        // ------------------------------ B step: cells with c + r = s + 1 on the odd diagonals ---------------
+        if (r + 1 >= 1 && r + 1 <= lb) load_run(subA, r + 1, 2 * g);
+        // ------------------------------ block B ----------------------------------------------------------------
         {
-            int const c = (s + 1 + dA + 1) >> 1, r = (s + 1 - dA - 1) >> 1;
-            bool const valid = (c | r) >= 0 && c <= la && r <= lb;
-            int32_t Vu = __shfl_down_sync(kFull, VA, 1, L);
-            int32_t Su = __shfl_down_sync(kFull, SA, 1, L);
-            if (l == L - 1)
+            int32_t sU = __shfl_down_sync(kFull, SA[0], 1, G);
+            int32_t vU = __shfl_down_sync(kFull, VA[0], 1, G);
+            if (g == G - 1)
             {
-                // upper neighbour (c, r-1) lies in region U, right of the boundary cell (c-1, r-1) = (SB, HB)
-                Vu = kBandNeg; Su = kBandNeg;
-                if (r >= 1 && c - 1 <= la && r - 1 <= lb)
+                // the upper neighbour (c, r-1) of the run's last cell lies in region U, right of the boundary cell
+                // (c-1, r-1) = latest cell of diagonal dHi = (SB[Q-1], HB); row lb is closed in iteration r = lb + 1
+                int const c = r + dLo + W - 1;
+                sU = kBandNeg; vU = kBandNeg;
+                if (live && r >= 1 && r - 1 <= lb && c - 1 <= la)
                 {
-                    int32_t const th = HB + ge, ts = SB + go;
-                    int32_t const Hu = max(th, ts);                              // first U cell of row r-1
-                    Vu = (r - 1 >= 1) ? (c + r - 2) * ge + go + runU : kBandNeg;
-                    Su = max(Vu, Hu);
+                    int32_t const th = HB + ge, ts = SB[Q - 1] + go;
+                    int32_t const hu = max(th, ts);                              // first U cell of row r-1
+                    vU = (r - 1 >= 1) ? (c + r - 2) * ge + go + runU : kBandNeg;
+                    sU = max(vU, hu);
                     uTH[r - 1] = th - c * ge; uTS[r - 1] = ts - c * ge; uM[r - 1] = runU;
-                    runU = max(runU, Hu - c * ge - (r - 1) * ge);
+                    runU = max(runU, hu - c * ge - (r - 1) * ge);
                 }
             }
-            int32_t const dd = SB + subB;
-            int32_t const h = max_push(HA + ge, SA + go, tw);
-            int32_t const v = max_push(Vu + ge, Su + go, tw);
-            int32_t const g = max_push(v, h, tw);
-            int32_t const sc = max_push(dd, g, tw);
-            if (valid) { SB = sc; HB = h; VB = v; }
-            if (valid && c == la && r == lb)
+            if (rowValid)
             {
-                PairState & st = state[p];
-                st.currentUpper = sc; st.sEnd = sc; st.vEnd = v; st.hEnd = h;
+                uint32_t tw[TW];
+                #pragma unroll
+                for (int k = 0; k < TW; ++k) tw[k] = 0u;
+                if (r == lb && bEnd == 2 * g + 1)
+                    HB = band_run<Q, true>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, tw, jEnd, sE, vE, hE);
+                else
+                    HB = band_run<Q, false>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, tw, 0, sE, vE, hE);
+                store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g + 1)) * PPW + q, tw);
             }
         }
-        if ((s & 7) == 6 && live && s < d.nSpad)
-            trace[(size_t)(s >> 3) * L] = (int32_t)tw;
-        subA = nextA; subB = nextB;
+    }
+    if (bEnd >= 0 && (bEnd >> 1) == g)
+    {
+        PairState & st = state[p];
+        st.currentUpper = sE; st.sEnd = sE; st.vEnd = vE; st.hEnd = hE;
     }
 }
 
-template <int L>
-cudaError_t launch_l(int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
-                     int32_t go, int32_t ge, cudaStream_t stream)
+template <int G, int Q>
+cudaError_t launch_gq(int nSlots, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
+                      int32_t go, int32_t ge, cudaStream_t stream)
 {
-    int const pairsPerBlock = 4 * (32 / L);
-    int const blocks = (n + pairsPerBlock - 1) / pairsPerBlock;
-    gotoh_band_kernel<L><<<blocks, 128, 0, stream>>>(n, pairIdx, desc, state, arena, go, ge);
+    int const slotsPerBlock = 4 * (32 / G);
+    int const blocks = (nSlots + slotsPerBlock - 1) / slotsPerBlock;
+    gotoh_band_kernel<G, Q><<<blocks, 128, 0, stream>>>(nSlots, pairIdx, desc, state, arena, go, ge);
     return cudaGetLastError();
 }
 
 } // namespace
 
-cudaError_t launch_gotoh_band(int L, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
+bool band_shape_supported(int G, int Q)
+{
+    if (Q == 16) return G == 1 || G == 2 || G == 4 || G == 8 || G == 16 || G == 32;
+    if (Q == 4) return G == 4 || G == 8 || G == 16 || G == 32;
+    return false;
+}
+
+cudaError_t launch_gotoh_band(int G, int Q, int nSlots, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t go, int32_t ge, cudaStream_t stream)
 {
-    if (n <= 0)
+    if (nSlots <= 0)
         return cudaSuccess;
-    if (L == 16) return launch_l<16>(n, pairIdx, desc, state, arena, go, ge, stream);
-    if (L == 32) return launch_l<32>(n, pairIdx, desc, state, arena, go, ge, stream);
+#define LARA_GQ(g_, q_) if (G == g_ && Q == q_) return launch_gq<g_, q_>(nSlots, pairIdx, desc, state, arena, go, ge, stream);
+    LARA_GQ(1, 16) LARA_GQ(2, 16) LARA_GQ(4, 16) LARA_GQ(8, 16) LARA_GQ(16, 16) LARA_GQ(32, 16)
+    LARA_GQ(4, 4) LARA_GQ(8, 4) LARA_GQ(16, 4) LARA_GQ(32, 4)
+#undef LARA_GQ
     return cudaErrorInvalidValue;
 }
 

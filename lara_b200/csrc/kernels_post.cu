@@ -235,9 +235,10 @@ __device__ int traceback_walk(PairDesc const & d, PairState const & st, int32_t 
 // forms of the pure gap regions U (c - r > dHi) and L (c - r < dLo); see tools/band_proto.py (u_nib / l_nib).
 struct BandView
 {
-    int la, lb, dLo, dHi, L;
+    int la, lb, dLo, dHi;
+    int W, Q, ppw, slot;                    // band geometry and position in the warp group (lara_gpu.cuh: PairDesc)
     int32_t go, ge;
-    int32_t const * trace;
+    uint16_t const * trace;                 // group base of the trace, in half words (4 nibbles each)
     int32_t const * uTH, * uTS, * uM;      // per row
     int32_t const * lTV, * lTS, * lM;      // per column
 };
@@ -305,11 +306,12 @@ __device__ void band_end_values(BandView const & v, int32_t & sE, int32_t & vE, 
 }
 
 // Traceback + evaluateLines for band mode: the segment walker of traceback_walk over a polymorphic cell fetch.
-// Window = the 8 trace word rows (64 anti-diagonal steps) ending at the walker's step, in shared memory.
+// Window = 32 rows x 32 band diagonals around the walker, in shared memory: lane i fetches row rHi - i as eight
+// half words (4 nibbles each) and packs them into win[4 i .. 4 i + 3], nibble x of the window at bits 4 (x % 8)
+// of word x / 8.
 __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, int32_t hEnd, uint32_t * linesRev,
                               uint32_t * win, int32_t & gapOut, int lane)
 {
-    int const L = v.L;
     int32_t const go = v.go, ge = v.ge;
     int c = v.la, r = v.lb;
     int n = 0;
@@ -317,15 +319,41 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
     int prev = 0, state = 0;
     int endFix = (vEnd == sEnd) ? 1 : ((hEnd == sEnd) ? 2 : 0);
     bool first = true;
+    int const nUnits = v.W / v.Q;
     while (c > 0 && r > 0)
     {
-        // ---- window: trace word rows [rowLo, rowHi], rowHi = (c + r) >> 3 -------------------------------------
-        int const rowHi = (c + r) >> 3, rowLo = max(rowHi - 7, 0);
-        __syncwarp();
-        for (int i = lane; i < 8 * L; i += 32)
+        // ---- window: rows [rHi - 31, rHi], diagonal indices [xLo, xLo + 32) ----------------------------------
+        int const rHi = r;
+        int xLo = 0;
+        if (v.W > 32)
         {
-            int const row = rowLo + i / L;
-            win[i] = row <= rowHi ? (uint32_t)__ldg(v.trace + (size_t)row * L + (i % L)) : 0u;
+            int const x = min(max(c - r - v.dLo, 0), v.W - 1);
+            xLo = min(max((x - 8) & ~15, 0), v.W - 32);
+        }
+        __syncwarp();
+        {
+            int const rr = rHi - lane;
+            uint32_t w[4] = {0u, 0u, 0u, 0u};
+            if (rr >= 1)
+            {
+                if (v.Q == 16)
+                {
+                    // units of 16 nibbles (8 bytes); xLo is a multiple of 16
+                    uint2 const * __restrict__ src = reinterpret_cast<uint2 const *>(v.trace) +
+                                                     ((size_t)rr * nUnits + (xLo >> 4)) * v.ppw + v.slot;
+                    uint2 const u0 = __ldg(src), u1 = __ldg(src + v.ppw);
+                    w[0] = u0.x; w[1] = u0.y; w[2] = u1.x; w[3] = u1.y;
+                }
+                else
+                {
+                    // units of 4 nibbles (one half word)
+                    uint16_t const * __restrict__ src = v.trace + ((size_t)rr * nUnits + (xLo >> 2)) * v.ppw + v.slot;
+                    #pragma unroll
+                    for (int h = 0; h < 8; ++h)
+                        w[h >> 1] |= (uint32_t)__ldg(src + (size_t)h * v.ppw) << (16 * (h & 1));
+                }
+            }
+            *reinterpret_cast<uint4 *>(win + 4 * lane) = make_uint4(w[0], w[1], w[2], w[3]);
         }
         __syncwarp();
         // known(ci, ri): the trace decision of that cell can be evaluated now
@@ -335,17 +363,17 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             if (ci < 1 || ri < 1) return 0u;
             int const dd = ci - ri;
             if (dd > v.dHi || dd < v.dLo) { known = true; return band_outside_nib(v, ci, ri); }
-            int const s = ci + ri, row = s >> 3;
-            if (row < rowLo) return 0u;
+            int const x = dd - v.dLo - xLo, row = rHi - ri;
+            if (row > 31 || x < 0 || x > 31) return 0u;
             known = true;
-            return (win[(row - rowLo) * L + ((dd - v.dLo) >> 1)] >> (4 * (7 - (s & 7)))) & 15u;
+            return (win[4 * row + (x >> 3)] >> (4 * (x & 7))) & 15u;
         };
         for (;;)
         {
             if (c <= 0 || r <= 0) break;
             {
-                int const dd = c - r;
-                if (dd <= v.dHi && dd >= v.dLo && ((c + r) >> 3) < rowLo) break;     // current cell left the window
+                int const dd = c - r, x = dd - v.dLo - xLo;
+                if (dd <= v.dHi && dd >= v.dLo && (rHi - r > 31 || x < 0 || x > 31)) break;   // current cell left the window
             }
             if (state == 0)
             {
@@ -543,7 +571,9 @@ __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __res
     uint32_t const * bits = (uint32_t const *)(arena + d.offBits) + (size_t)a * d.bitWords;
     int e = arena[d.offRowStart + a];
     int const wb = b >> 5;
-    for (int w = 0; w < wb; ++w) e += __popc(bits[w]);
+    // band mode: every active cell of row a lies at b >= a - dHi, the words before it are empty
+    int const w0 = d.bandW > 0 ? (max(a - d.dHi, 0) >> 5) : 0;
+    for (int w = w0; w < wb; ++w) e += __popc(bits[w]);
     uint32_t const word = bits[wb];
     if (!((word >> (b & 31)) & 1u)) return -1;
     return e + __popc(word & ((1u << (b & 31)) - 1u));
@@ -587,11 +617,12 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     // ---- 1. traceback + evaluateLines ------------------------------------------------------------
     int32_t gapScore = 0;
     int nLines;
-    if (d.bandL > 0)
+    if (d.bandW > 0)
     {
         BandView bv;
-        bv.la = d.la; bv.lb = d.lb; bv.dLo = d.dLo; bv.dHi = d.dHi; bv.L = d.bandL; bv.go = P.go; bv.ge = P.ge;
-        bv.trace = arena + d.offBTrace;
+        bv.la = d.la; bv.lb = d.lb; bv.dLo = d.dLo; bv.dHi = d.dHi; bv.go = P.go; bv.ge = P.ge;
+        bv.W = d.bandW; bv.Q = d.bandQ; bv.ppw = 32 / d.bandG; bv.slot = d.bandSlot;
+        bv.trace = reinterpret_cast<uint16_t const *>(arena + d.offBTrace);
         bv.uTH = arena + d.offU; bv.uTS = bv.uTH + (d.lb + 1); bv.uM = bv.uTS + (d.lb + 1);
         bv.lTV = arena + d.offL; bv.lTS = bv.lTV + (d.la + 1); bv.lM = bv.lTS + (d.la + 1);
         int32_t sE = st.sEnd, vE = st.vEnd, hE = st.hEnd;
@@ -629,6 +660,8 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     int32_t * __restrict__ dual = arena + d.offDual;
     int32_t const * __restrict__ rev = arena + d.offRev;
     int32_t * __restrict__ list = arena + d.offList;
+    // candidates are collected in shared memory when their upper bound fits, else in the pair's global buffer
+    // (and moved to shared memory for the sort when the actual number fits)
     bool const candInSmem = d.kCap <= smemCand;
     unsigned long long * cand = candInSmem ? sm.cand : (unsigned long long *)(arena + d.offCand);
 
@@ -687,6 +720,12 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     __syncwarp();
     int const nList = sm.misc[0];
     int const nCand = min(sm.misc[1], d.kCap);
+    if (!candInSmem && nCand <= smemCand)
+    {
+        for (int i = lane; i < nCand; i += 32) sm.cand[i] = cand[i];
+        cand = sm.cand;
+        __syncwarp();
+    }
 
     // ---- 4. structural part of the lower bound ---------------------------------------------------
     int32_t lbStruct = 0;
@@ -788,7 +827,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     if (!finished)
     {
         // ---- 8a. updateScores (:312-323): refresh the queue top of every touched edge -------------
-        int32_t * __restrict__ vals = arena + d.offVals;
+        int32_t * __restrict__ vals = arena + (d.bandW > 0 ? d.offBVals : d.offVals);
         int32_t const * __restrict__ perm = arena + d.offPerm;
         for (int i = lane; i < nList; i += 32)
         {

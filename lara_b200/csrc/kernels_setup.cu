@@ -312,10 +312,10 @@ setup_count_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__
     if (lane == 0) { ioff[E] = carry; d.D = carry; }
 
     // 4. geometry of the value stream
-    if (d.bandL > 0)
+    if (d.bandW > 0)
     {
-        // band mode: dense band stream vals[s * bandL + lane]
-        if (lane == 0) d.nVals = d.nSpad * d.bandL;
+        // band mode: the dense band array of the pair's warp group is laid out by the host (offBVals)
+        if (lane == 0) d.nVals = 0;
         return;
     }
     // full-matrix mode: strip-dense stream: step flags per lane, stream start per lane
@@ -394,17 +394,22 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
     // 3. value stream + permutation
     int32_t * __restrict__ vals = arena + d.offVals;
     int32_t * __restrict__ perm = arena + d.offPerm;
-    if (d.bandL > 0)
+    if (d.bandW > 0)
     {
-        // band mode: cell (a, b) = matrix cell (c, r) = (a + 1, b + 1) sits at step s = c + r on diagonal a - b
+        // band mode: matrix cell (c, r) = (a + 1, b + 1) sits in row r at diagonal index x = a - b - dLo of the
+        // group's interleaved band array (lara_gpu.cuh: band_val_index); rows 1..lb of this pair's slot
+        int const ppw = 32 / d.bandG, nch = d.bandW >> 2;
+        int4 * __restrict__ bv = reinterpret_cast<int4 *>(arena + d.offBVals) + d.bandSlot;
         __syncwarp();
-        for (int i = lane; i < d.nVals; i += 32) vals[i] = kDpNeg;
+        for (int i = lane; i < lb * nch; i += 32)
+            bv[((size_t)nch + (size_t)i) * ppw] = make_int4(kDpNeg, kDpNeg, kDpNeg, kDpNeg);
         __syncwarp();
+        vals = arena + d.offBVals;
         for (int e = lane; e < E; e += 32)
         {
             int const ab = cell[e];
             int const a = ab >> 16, b = ab & 0xffff;
-            int const idx = (a + b + 2) * d.bandL + ((a - b - d.dLo) >> 1);
+            int const idx = (int)band_val_index(d.bandW, ppw, d.bandSlot, b + 1, a - b - d.dLo);
             vals[idx] = pv[e];
             perm[e] = idx;
         }

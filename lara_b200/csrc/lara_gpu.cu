@@ -53,6 +53,10 @@ struct Worker
     int32_t * hActive = nullptr;            // pinned
     std::vector<cudaEvent_t> events;
     cudaEvent_t evDone = nullptr;
+    // side streams: the DP launches of the smaller kernel classes of an iteration run beside the largest one
+    std::vector<cudaStream_t> aux;
+    std::vector<cudaEvent_t> auxJoin;
+    cudaEvent_t evFork = nullptr;
     lara_stats stats{};
     std::string err;
 };
@@ -90,9 +94,13 @@ struct lara_ctx
     std::string err;
     std::deque<Device> devs;                // deque: Device holds a mutex and is not movable
     int nWorkers = 3;                       // concurrent batches per device (env LARA_B200_WORKERS)
-    size_t batchPairsDefault = 8192;        // pairs per batch (env LARA_B200_BATCH)
+    size_t batchPairsDefault = 32768;       // pairs per batch (env LARA_B200_BATCH)
     bool bandMode = true;                   // band DP kernels where the active edges allow it (env LARA_B200_BAND=0: off)
     int bandMargin = 1;                     // diagonals added on both sides of the active range (env LARA_B200_MARGIN)
+    int bandMaxW = 1024;                    // widest band; beyond it the full-matrix kernel runs (env LARA_B200_BANDMAXW)
+    int bandMinWarps = 592;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
+    int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
+    int postSmemCand = 256;                 // matching candidates sorted in shared memory (env LARA_B200_SMEMCAND)
     // host copy of the inputs (for pair orientation and batch sizing)
     int32_t nSeq = 0;
     std::vector<int64_t> seqOff, bpOff;
@@ -168,12 +176,12 @@ double ev_ms(cudaEvent_t a, cudaEvent_t b)
     return (double)ms;
 }
 
-// Band geometry of one pair from the diagonal range of its active edges (kernels_band.cu): dLo even,
-// dLo <= 0 <= dHi, 2 * bandL diagonals.  bandL = 0 selects the full-matrix kernel (band wider than 64
+// Band geometry of one pair from the diagonal range of its active edges (kernels_band.cu): dLo <= 0 <= dHi,
+// bandW = 32 .. 1024 diagonals (multiple of 32).  bandW = 0 selects the full-matrix kernel (band wider than 1024
 // diagonals, or gap costs outside the band kernel's precondition go < ge).
 void choose_band(lara_ctx const & ctx, PairDesc & d)
 {
-    d.bandL = 0; d.dLo = 0; d.dHi = -1; d.nSpad = 0;
+    d.bandW = 0; d.bandG = 0; d.bandQ = 0; d.bandSlot = 0; d.dLo = 0; d.dHi = -1;
     if (!ctx.bandMode || !(ctx.dp.go < ctx.dp.ge)) return;
     int lo = 0, hi = 0;
     if (d.E > 0 && d.dMin <= d.dMax)
@@ -181,12 +189,26 @@ void choose_band(lara_ctx const & ctx, PairDesc & d)
         lo = std::min(d.dMin - ctx.bandMargin, 0);
         hi = std::max(d.dMax + ctx.bandMargin, 0);
     }
-    if (lo & 1) lo -= 1;
     int const need = hi - lo + 1;
-    int const L = need <= 32 ? 16 : (need <= 64 ? 32 : 0);
-    if (L == 0) return;
-    d.bandL = L; d.dLo = lo; d.dHi = lo + 2 * L - 1;
-    d.nSpad = (d.la + d.lb + 3 + 7) & ~7;
+    int W = 32;
+    while (W < need) W <<= 1;
+    if (W > ctx.bandMaxW) return;
+    // a band that needs the full-matrix kernel's work or more is not worth it (short sequences)
+    if (d.lb <= 32 * kMaxR && (int64_t)W * (d.lb + 1) >= (int64_t)d.la * d.lb) return;
+    int const slack = W - need;
+    lo -= std::min(slack / 2, std::max(0, d.lb + lo));          // spare diagonals: both sides, none below -lb
+    d.bandW = W; d.dLo = lo; d.dHi = lo + W - 1;
+}
+
+// Lanes per pair G and diagonals per block Q for the nPairs pairs of a batch that share the band width W:
+// Q = 16 (G = W / 32, down to one thread per pair) when that still fills the machine, else Q = 4 (G = W / 8).
+void choose_band_shape(lara_ctx const & ctx, int W, int nPairs, int & G, int & Q)
+{
+    int const g16 = W / 32, g4 = W / 8;
+    int64_t const warps16 = ((int64_t)nPairs * g16 + 31) / 32;
+    Q = (g4 > 32 || warps16 >= ctx.bandMinWarps) ? 16 : 4;
+    if (ctx.bandForceQ == 16 || (ctx.bandForceQ == 4 && g4 <= 32)) Q = ctx.bandForceQ;
+    G = Q == 16 ? g16 : g4;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -218,16 +240,15 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
                 d.kCap = std::min(ctx.nbp[op.first], ctx.nbp[op.second]) + 1;
                 maxLa = std::max(maxLa, d.la); maxLb = std::max(maxLb, d.lb); maxK = std::max(maxK, d.kCap);
             }
-            int64_t const nFlagWords = (d.nSteps + 31) / 32;
             d.offBits = rg.take((int64_t)d.la * d.bitWords);
             d.offRowStart = rg.take(d.la + 1);
-            d.offFlags = rg.take(32 * nFlagWords);
-            d.offLanePtr = rg.take(32);
-            d.offTrace = rg.take(32ll * d.nSteps * d.W);
             d.offLines = rg.take(d.lb);
             d.offBest = rg.take(d.lb);
-            d.offCand = rg.take(2ll * d.kCap);
-            d.offScratch = rg.take((int64_t)d.la * d.lb + 6ll * (d.la + 1));
+            {
+                int64_t capPow2 = 32;                   // the bitonic sort pads to a power of two
+                while (capPow2 < d.kCap) capPow2 <<= 1;
+                d.offCand = rg.take(2 * capPow2);
+            }
         }
     };
     {
@@ -241,6 +262,17 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     int32_t * const arena = rA.ptr;
     layoutA(true, rA);
 
+    // edge filter scratch (forward prefix scores): its own allocation, released right after stage 1
+    Region rS;
+    {
+        int64_t sizeS = 0;
+        for (int i = 0; i < n; ++i) sizeS += align4((int64_t)desc[(size_t)i].la * desc[(size_t)i].lb + 6ll * (desc[(size_t)i].la + 1));
+        CK(cudaMallocAsync((void **)&rS.ptr, (size_t)sizeS * 4, s));
+        rS.size = sizeS; rS.baseDelta = rS.ptr - arena;
+        for (int i = 0; i < n; ++i)
+            desc[(size_t)i].offScratch = rS.take((int64_t)desc[(size_t)i].la * desc[(size_t)i].lb + 6ll * (desc[(size_t)i].la + 1));
+    }
+
     PairDesc * dDesc = nullptr;
     PairState * dState = nullptr;
     CK(cudaMallocAsync((void **)&dDesc, sizeof(PairDesc) * (size_t)n, s));
@@ -253,18 +285,66 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     // ---- stage 1: edge filter -> E ------------------------------------------------------------------
     CK(launch_edge_filter(n, dDesc, dState, arena, dv.in, dp, s));
     CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaFreeAsync(rS.ptr, s));
     CK(cudaStreamSynchronize(s));
     wk.stats.kernel_launches += 1;
-    // ---- stage B layout: per-edge arrays ---------------------------------------------------------------
+    // ---- stage B layout: per-edge arrays, band geometry and warp groups of the band kernels --------------------
+    std::map<int, std::vector<int32_t>> byW;               // band width -> pairs
+    for (int i = 0; i < n; ++i)
+    {
+        choose_band(ctx, desc[(size_t)i]);
+        if (desc[(size_t)i].bandW > 0) byW[desc[(size_t)i].bandW].push_back(i);
+    }
+    struct BandClass { int G, Q; std::vector<int32_t> slots; };    // slots: pair index or -1, 32 / G per warp group
+    std::vector<BandClass> bandClasses;
+    struct BandGroup { int W, ppw, rows, first, count; int cls; };
+    std::vector<BandGroup> groups;
+    for (auto & kv : byW)
+    {
+        int const W = kv.first;
+        std::vector<int32_t> & members = kv.second;
+        std::stable_sort(members.begin(), members.end(), [&](int32_t x, int32_t y) { return desc[(size_t)x].lb > desc[(size_t)y].lb; });
+        int G, Q;
+        choose_band_shape(ctx, W, (int)members.size(), G, Q);
+        int ci = -1;
+        for (size_t k = 0; k < bandClasses.size(); ++k) if (bandClasses[k].G == G && bandClasses[k].Q == Q) ci = (int)k;
+        if (ci < 0) { bandClasses.push_back(BandClass{G, Q, {}}); ci = (int)bandClasses.size() - 1; }
+        int const ppw = 32 / G;
+        for (size_t k = 0; k < members.size(); k += (size_t)ppw)
+        {
+            int const cnt = (int)std::min<size_t>((size_t)ppw, members.size() - k);
+            groups.push_back(BandGroup{W, ppw, desc[(size_t)members[k]].lb + 1, (int)bandClasses[(size_t)ci].slots.size(), cnt, ci});
+            for (int j = 0; j < ppw; ++j)
+            {
+                if (j < cnt)
+                {
+                    PairDesc & d = desc[(size_t)members[k + (size_t)j]];
+                    d.bandG = G; d.bandQ = Q; d.bandSlot = j;
+                    bandClasses[(size_t)ci].slots.push_back(members[k + (size_t)j]);
+                }
+                else
+                    bandClasses[(size_t)ci].slots.push_back(-1);
+            }
+        }
+    }
     int64_t sizeB = 0;
     for (int i = 0; i < n; ++i)
     {
         PairDesc & d = desc[(size_t)i];
-        choose_band(ctx, d);
         sizeB += 4 * align4(std::max(d.E, 1)) + align4(d.E + 1);
-        if (d.bandL > 0)
-            sizeB += align4((int64_t)d.nSpad / 8 * d.bandL) + align4(3ll * (d.lb + 1)) + align4(3ll * (d.la + 1));
+        if (d.bandW > 0)
+            sizeB += align4(3ll * (d.lb + 1)) + align4(3ll * (d.la + 1));
+        else
+        {
+            if (d.R > kMaxR)
+                throw std::runtime_error("a pair whose shorter sequence exceeds " + std::to_string(32 * kMaxR) +
+                                         " nt has active edges on more than " + std::to_string(ctx.bandMaxW) +
+                                         " diagonals: outside the band kernels and the single-pass full-matrix kernel");
+            sizeB += align4(32ll * ((d.nSteps + 31) / 32)) + 32 + align4(32ll * d.nSteps * d.W);
+        }
     }
+    for (BandGroup const & g : groups)
+        sizeB += align4((int64_t)g.rows * g.W * g.ppw) + align4((int64_t)g.rows * (g.W / 8) * g.ppw);
     Region rB;
     CK(cudaMallocAsync((void **)&rB.ptr, (size_t)sizeB * 4, s));
     rB.size = sizeB; rB.baseDelta = rB.ptr - arena;
@@ -273,12 +353,29 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         PairDesc & d = desc[(size_t)i];
         d.offCell = rB.take(d.E); d.offSeqScore = rB.take(d.E); d.offPv = rB.take(d.E); d.offPerm = rB.take(d.E);
         d.offIoff = rB.take(d.E + 1);
-        if (d.bandL > 0)
+        if (d.bandW > 0)
         {
-            d.offBTrace = rB.take((int64_t)d.nSpad / 8 * d.bandL);
             d.offU = rB.take(3ll * (d.lb + 1));
             d.offL = rB.take(3ll * (d.la + 1));
             ++wk.stats.reserved[1];                     // pairs solved by the band kernels
+            if (d.bandQ == 16) ++wk.stats.reserved[2];  // ... of those in blocks of 16 diagonals
+            wk.stats.reserved[3] += d.bandW;            // sum of their band widths
+        }
+        else
+        {
+            d.offFlags = rB.take(32ll * ((d.nSteps + 31) / 32));
+            d.offLanePtr = rB.take(32);
+            d.offTrace = rB.take(32ll * d.nSteps * d.W);
+        }
+    }
+    for (BandGroup const & g : groups)
+    {
+        int64_t const ov = rB.take((int64_t)g.rows * g.W * g.ppw);
+        int64_t const ot = rB.take((int64_t)g.rows * (g.W / 8) * g.ppw);
+        for (int j = 0; j < g.count; ++j)
+        {
+            PairDesc & d = desc[(size_t)bandClasses[(size_t)g.cls].slots[(size_t)(g.first + j)]];
+            d.offBVals = ov; d.offBTrace = ot;
         }
     }
     CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
@@ -306,27 +403,40 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     wk.stats.kernel_launches += 1;
     CK(cudaEventRecord(evS1, s));
 
-    // ---- rows-per-lane classes for the DP launches -------------------------------------------------------------
-    // class key: rows per lane R (full-matrix kernel) or -bandL (band kernel)
+    // ---- launch classes of the DP: rows per lane R (full-matrix kernel) or band shape (G, Q) ----------------------
     std::map<int, std::vector<int32_t>> classes;
     for (int i = 0; i < n; ++i)
-        classes[desc[(size_t)i].bandL > 0 ? -desc[(size_t)i].bandL : desc[(size_t)i].R].push_back(i);
+        if (desc[(size_t)i].bandW == 0) classes[desc[(size_t)i].R].push_back(i);
     std::vector<int32_t> idxAll;
-    std::vector<std::tuple<int, int, int>> cls;        // R, offset, count
+    std::vector<std::tuple<int, int, int, int>> cls;   // R (or 0), offset, count, band class
     for (auto & kv : classes)
     {
-        cls.emplace_back(kv.first, (int)idxAll.size(), (int)kv.second.size());
+        cls.emplace_back(kv.first, (int)idxAll.size(), (int)kv.second.size(), -1);
         idxAll.insert(idxAll.end(), kv.second.begin(), kv.second.end());
     }
+    for (size_t k = 0; k < bandClasses.size(); ++k)
+    {
+        cls.emplace_back(0, (int)idxAll.size(), (int)bandClasses[k].slots.size(), (int)k);
+        idxAll.insert(idxAll.end(), bandClasses[k].slots.begin(), bandClasses[k].slots.end());
+    }
+    std::stable_sort(cls.begin(), cls.end(), [](auto const & x, auto const & y) { return std::get<2>(x) > std::get<2>(y); });
+    if (!wk.evFork) CK(cudaEventCreateWithFlags(&wk.evFork, cudaEventDisableTiming));
+    while (wk.aux.size() + 1 < cls.size())
+    {
+        cudaStream_t st; cudaEvent_t ev;
+        CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        wk.aux.push_back(st); wk.auxJoin.push_back(ev);
+    }
     int32_t * dIdx = nullptr;
-    CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * idxAll.size(), s));
+    CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * std::max<size_t>(idxAll.size(), 1), s));
     CK(cudaMemcpyAsync(dIdx, idxAll.data(), sizeof(int32_t) * idxAll.size(), cudaMemcpyHostToDevice, s));
     *wk.hActive = n;
     CK(cudaMemcpyAsync(wk.dActive, wk.hActive, sizeof(int32_t), cudaMemcpyHostToDevice, s));
 
     // shared memory candidates: as many as fit next to the line arrays (cap 2048)
     int smemCand = 32;
-    while (smemCand < maxK && smemCand < 2048) smemCand <<= 1;
+    while (smemCand < maxK && smemCand < ctx.postSmemCand) smemCand <<= 1;
 
     // ---- the subgradient loop -------------------------------------------------------------------------------------
     int const nIter = ctx.P.num_iterations;
@@ -342,16 +452,23 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     for (int it = 0; it < nIter; ++it)
     {
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it], s));
-        for (auto const & c : cls)
+        // the largest class on the worker's stream, the others beside it on side streams (fork / join by events)
+        if (cls.size() > 1) CK(cudaEventRecord(wk.evFork, s));
+        for (size_t k = 0; k < cls.size(); ++k)
         {
-            if (std::get<0>(c) < 0)
-                CK(launch_gotoh_band(-std::get<0>(c), std::get<2>(c), dIdx + std::get<1>(c), dDesc, dState, arena,
-                                     dp.go, dp.ge, s));
+            auto const & c = cls[k];
+            cudaStream_t const sk = k == 0 ? s : wk.aux[k - 1];
+            if (k > 0) CK(cudaStreamWaitEvent(sk, wk.evFork, 0));
+            if (std::get<3>(c) >= 0)
+                CK(launch_gotoh_band(bandClasses[(size_t)std::get<3>(c)].G, bandClasses[(size_t)std::get<3>(c)].Q, std::get<2>(c),
+                                     dIdx + std::get<1>(c), dDesc, dState, arena, dp.go, dp.ge, sk));
             else
                 CK(launch_gotoh_fill(std::get<0>(c), std::get<2>(c), dIdx + std::get<1>(c), dDesc, dState, arena, dv.negBuf,
-                                     dp.go, dp.ge, s));
+                                     dp.go, dp.ge, sk));
+            if (k > 0) CK(cudaEventRecord(wk.auxJoin[k - 1], sk));
             wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
         }
+        for (size_t k = 1; k < cls.size(); ++k) CK(cudaStreamWaitEvent(s, wk.auxJoin[k - 1], 0));
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 1], s));
         CK(launch_iterate_post(n, dDesc, dState, arena, dp, dv.dOutHdr + begin, dv.dOutLines, dv.dOutOff + begin,
                                wk.dActive, maxLa, maxLb, smemCand, s));
@@ -402,7 +519,7 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers)
 {
     size_t freeB = 0, totalB = 0;
     cudaMemGetInfo(&freeB, &totalB);
-    double const budget = 0.45 * (double)totalB / (double)nWorkers;
+    double const budget = 0.6 * (double)totalB / (double)nWorkers;
     double used = 0;
     size_t k = begin;
     size_t const hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : ctx.batchPairsDefault;
@@ -410,7 +527,9 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers)
     {
         OrientedPair const & op = dv.pairs[k];
         double const C = (double)op.la * op.lb;
-        double const per = 4.0 * (C + 32.0 * (op.la + 34) * 4 + 64 * op.la) + 48.0 * C;
+        // bytes: filter scratch 4 C (set-up only); bitmap, edges (E <= ~0.2 C, 5 arrays), interactions (D <= ~3 E,
+        // 6 arrays), band arrays or full-matrix trace, lines: generously 16 C + 3 KB per residue
+        double const per = 4.0 * C + 16.0 * C + 3072.0 * (op.la + op.lb);
         if (used + per > budget && k > begin) break;
         used += per;
         ++k;
@@ -484,7 +603,12 @@ void run_device(lara_ctx & ctx, Device & dv)
             dv.stats.n_active_edges += wk.stats.n_active_edges; dv.stats.n_interactions += wk.stats.n_interactions;
         }
         dv.stats.reserved[0] = nW;
-        for (int w = 0; w < nW; ++w) dv.stats.reserved[1] += dv.workers[(size_t)w].stats.reserved[1];
+        for (int w = 0; w < nW; ++w)
+        {
+            dv.stats.reserved[1] += dv.workers[(size_t)w].stats.reserved[1];
+            dv.stats.reserved[2] += dv.workers[(size_t)w].stats.reserved[2];
+            dv.stats.reserved[3] += dv.workers[(size_t)w].stats.reserved[3];
+        }
     }
     catch (std::exception const & e)
     {
@@ -548,6 +672,10 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_WORKERS")) ctx->nWorkers = std::max(1, std::min(8, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BAND")) ctx->bandMode = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_MARGIN")) ctx->bandMargin = std::max(0, std::min(16, std::atoi(e)));
+    if (char const * e = std::getenv("LARA_B200_BANDMAXW")) ctx->bandMaxW = std::max(0, std::min(1024, std::atoi(e)));
+    if (char const * e = std::getenv("LARA_B200_BANDMINWARPS")) ctx->bandMinWarps = std::max(1, std::atoi(e));
+    if (char const * e = std::getenv("LARA_B200_BANDQ")) ctx->bandForceQ = std::atoi(e);
+    if (char const * e = std::getenv("LARA_B200_SMEMCAND")) ctx->postSmemCand = std::max(32, std::min(2048, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
     ctx->P = *params;
     ctx->dp = make_dev_params(*params);
@@ -628,6 +756,9 @@ void lara_gpu_destroy(lara_ctx * ctx)
             if (wk.hActive) cudaFreeHost(wk.hActive);
             for (cudaEvent_t ev : wk.events) cudaEventDestroy(ev);
             if (wk.evDone) cudaEventDestroy(wk.evDone);
+            if (wk.evFork) cudaEventDestroy(wk.evFork);
+            for (cudaEvent_t ev : wk.auxJoin) cudaEventDestroy(ev);
+            for (cudaStream_t st : wk.aux) cudaStreamDestroy(st);
             if (wk.stream) cudaStreamDestroy(wk.stream);
         }
     }
@@ -713,9 +844,11 @@ int lara_gpu_prepare_pairs(lara_ctx * ctx, int64_t n_pairs, int32_t const * idx_
         if (li >= lj) { op.first = i; op.second = j; op.la = li; op.lb = lj; }       // solver :117-120
         else { op.first = j; op.second = i; op.la = lj; op.lb = li; }
         op.request = p;
-        if ((op.lb + 31) / 32 > kMaxR)
+        if (op.la > 32767)
+            return set_err(ctx, LARA_E_UNSUPPORTED, "sequences longer than 32,767 nt are not supported (16-bit positions)");
+        if ((op.lb + 31) / 32 > kMaxR && !(ctx->bandMode && ctx->dp.go < ctx->dp.ge))
             return set_err(ctx, LARA_E_UNSUPPORTED, "shorter sequence of a pair exceeds " + std::to_string(32 * kMaxR) +
-                                                     " nt (single-pass DP limit of this build)");
+                                                     " nt (single-pass DP limit; the band kernels are switched off)");
     }
     // longest first, like the reference's queue (CompareSeqLength, src/io.hpp:352-365)
     std::stable_sort(all.begin(), all.end(), [](OrientedPair const & x, OrientedPair const & y) {
@@ -780,6 +913,8 @@ int lara_gpu_run_prepared(lara_ctx * ctx)
         agg.n_active_edges += dv.stats.n_active_edges; agg.n_interactions += dv.stats.n_interactions;
         agg.reserved[0] = std::max(agg.reserved[0], dv.stats.reserved[0]);     // concurrent workers per device
         agg.reserved[1] += dv.stats.reserved[1];                               // pairs solved by the band kernels
+        agg.reserved[2] += dv.stats.reserved[2];                               // ... in blocks of 16 diagonals
+        agg.reserved[3] += dv.stats.reserved[3];                               // sum of the band widths
     }
     agg.ms_total = ms;
     ctx->stats = agg;
@@ -972,40 +1107,48 @@ int lara_gpu_gotoh_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32
 }
 
 int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32_t lenB, int32_t const * pssm,
-                              int32_t d_lo, int32_t lanes, int32_t gap_open, int32_t gap_extend, int32_t * score,
-                              int32_t * n_lines, int32_t * lines_a, int32_t * lines_b, int32_t * gap_score)
+                              int32_t d_lo, int32_t band_width, int32_t lanes, int32_t gap_open, int32_t gap_extend,
+                              int32_t * score, int32_t * n_lines, int32_t * lines_a, int32_t * lines_b, int32_t * gap_score)
 {
     if (!ctx || !pssm || n_problems < 1 || lenA < 1 || lenB < 1) return set_err(ctx, LARA_E_INVALID, "bad argument");
-    if ((lanes != 16 && lanes != 32) || (d_lo & 1) || d_lo > 0 || d_lo + 2 * lanes - 1 < 0)
-        return set_err(ctx, LARA_E_INVALID, "band: lanes must be 16 or 32, d_lo even and d_lo <= 0 <= d_lo + 2 * lanes - 1");
+    int const G = lanes, W = band_width, Q = (G > 0 && W % (2 * G) == 0) ? W / (2 * G) : 0;
+    if (!band_shape_supported(G, Q) || d_lo > 0 || d_lo + W - 1 < 0)
+        return set_err(ctx, LARA_E_INVALID, "band: width / (2 * lanes) must be 16 (lanes 1..32) or 4 (lanes 4..32), "
+                                            "and d_lo <= 0 <= d_lo + width - 1");
     if (!(gap_open < gap_extend)) return set_err(ctx, LARA_E_UNSUPPORTED, "band kernel needs gap_open < gap_extend");
     Device & dv = ctx->devs[0];
     cudaStream_t const s = dv.stream;
-    int const n = n_problems, L = lanes, dHi = d_lo + 2 * L - 1;
+    int const n = n_problems, dHi = d_lo + W - 1, ppw = 32 / G;
+    int const nGroups = (n + ppw - 1) / ppw;
+    std::vector<int32_t> slots((size_t)nGroups * ppw, -1);
     try
     {
         CK(cudaSetDevice(dv.id));
         std::vector<PairDesc> desc((size_t)n);
         Region rg;
-        int const nSpad = (lenA + lenB + 3 + 7) & ~7;
         for (int pass = 0; pass < 2; ++pass)
         {
             rg.used = 0;
-            for (int i = 0; i < n; ++i)
+            for (int gi = 0; gi < nGroups; ++gi)
             {
-                PairDesc & d = desc[(size_t)i];
-                std::memset(&d, 0, sizeof(d));
-                d.la = lenA; d.lb = lenB; d.bandL = L; d.dLo = d_lo; d.dHi = dHi; d.nSpad = nSpad;
-                d.nVals = nSpad * L;
-                d.offVals = rg.take(d.nVals);
-                d.offBTrace = rg.take((int64_t)nSpad / 8 * L);
-                d.offU = rg.take(3ll * (lenB + 1));
-                d.offL = rg.take(3ll * (lenA + 1));
-                d.offLines = rg.take(lenB);
+                int64_t const ov = rg.take((int64_t)(lenB + 1) * W * ppw);
+                int64_t const ot = rg.take((int64_t)(lenB + 1) * (W / 8) * ppw);
+                for (int j = 0; j < ppw && gi * ppw + j < n; ++j)
+                {
+                    int const i = gi * ppw + j;
+                    PairDesc & d = desc[(size_t)i];
+                    std::memset(&d, 0, sizeof(d));
+                    d.la = lenA; d.lb = lenB; d.bandW = W; d.bandG = G; d.bandQ = Q; d.bandSlot = j; d.dLo = d_lo; d.dHi = dHi;
+                    d.offBVals = ov; d.offBTrace = ot;
+                    d.offU = rg.take(3ll * (lenB + 1));
+                    d.offL = rg.take(3ll * (lenA + 1));
+                    d.offLines = rg.take(lenB);
+                    slots[(size_t)i] = i;
+                }
             }
             if (pass == 0) CK(cudaMalloc((void **)&rg.ptr, (size_t)rg.used * 4));
         }
-        // dense band stream on the host: cell (a, b) -> step a + b + 2, lane (a - b - d_lo) >> 1
+        // dense band array on the host: cell (a, b) -> row b + 1, diagonal index a - b - d_lo
         std::vector<int32_t> host((size_t)rg.used, kDpNeg);
         for (int i = 0; i < n; ++i)
             for (int a = 0; a < lenA; ++a)
@@ -1018,7 +1161,8 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
                         cudaFree(rg.ptr);
                         return set_err(ctx, LARA_E_INVALID, "band: active cell outside the band");
                     }
-                    host[(size_t)desc[(size_t)i].offVals + (size_t)(a + b + 2) * L + ((a - b - d_lo) >> 1)] = v;
+                    PairDesc const & d = desc[(size_t)i];
+                    host[(size_t)(d.offBVals + band_val_index(W, ppw, d.bandSlot, b + 1, a - b - d_lo))] = v;
                 }
         int32_t * arena = rg.ptr;
         PairDesc * dDesc; PairState * dState;
@@ -1027,7 +1171,10 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
         CK(cudaMemcpyAsync(arena, host.data(), host.size() * 4, cudaMemcpyHostToDevice, s));
         CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
         CK(cudaMemsetAsync(dState, 0, sizeof(PairState) * (size_t)n, s));
-        CK(launch_gotoh_band(L, n, nullptr, dDesc, dState, arena, gap_open, gap_extend, s));
+        int32_t * dSlots;
+        CK(cudaMalloc((void **)&dSlots, slots.size() * 4));
+        CK(cudaMemcpyAsync(dSlots, slots.data(), slots.size() * 4, cudaMemcpyHostToDevice, s));
+        CK(launch_gotoh_band(G, Q, (int)slots.size(), dSlots, dDesc, dState, arena, gap_open, gap_extend, s));
         CK(launch_traceback_only(n, dDesc, dState, arena, gap_open, gap_extend, lenA, lenB, s));
         std::vector<PairState> hs((size_t)n);
         CK(cudaMemcpyAsync(hs.data(), dState, sizeof(PairState) * (size_t)n, cudaMemcpyDeviceToHost, s));
@@ -1048,7 +1195,7 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
                 if (lines_b) lines_b[(size_t)i * lenB + k] = (int32_t)(v & 0xffffu);
             }
         }
-        cudaFree(dState); cudaFree(dDesc); cudaFree(arena);
+        cudaFree(dSlots); cudaFree(dState); cudaFree(dDesc); cudaFree(arena);
     }
     catch (std::exception const & ex)
     {

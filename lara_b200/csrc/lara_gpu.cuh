@@ -79,10 +79,16 @@ struct PairDesc
     int64_t offScratch;         // set-up scratch: forward prefix scores [la * lb]
     // ---- band mode (kernels_band.cu): the DP runs only over the diagonals dLo <= c - r <= dHi ------------
     int32_t dMin, dMax;         // diagonal range (a - b) of the active edges (edge filter); dMin > dMax: none
-    int32_t bandL;              // lanes per pair of the band DP: 16 or 32 (band = 2 * bandL diagonals); 0 = full matrix
-    int32_t dLo, dHi;           // band (dLo even, dLo <= 0 <= dHi, dHi = dLo + 2 * bandL - 1)
-    int32_t nSpad;              // anti-diagonal steps of the band DP, multiple of 8 (>= la + lb + 3)
-    int64_t offBTrace;          // band trace: word [(s >> 3) * bandL + lane], nibble 7 - (s & 7)   [nSpad / 8 * bandL]
+    int32_t bandW;              // diagonals of the band = 2 * bandG * bandQ (multiple of 32); 0 = full-matrix kernel
+    int32_t bandG, bandQ;       // lanes per pair (32 / bandG pairs share a warp) and diagonals per block
+    int32_t bandSlot;           // position of the pair inside its warp group: 0 .. 32 / bandG - 1
+    int32_t dLo, dHi;           // band (dLo <= 0 <= dHi, dHi = dLo + bandW - 1)
+    // band arrays of the pair's warp group (PPW = 32 / bandG pairs, rows 0 .. max lb of the group), interleaved:
+    //   score of (row r, diagonal index x = c - r - dLo):  int  [((r * bandW/4 + x/4) * PPW + slot) * 4 + x%4]
+    //   trace nibble of the same cell: unit (r * 2 bandG + x / bandQ) * PPW + slot of bandQ nibbles (bandQ / 2 bytes),
+    //   nibble x % bandQ at bits 4 * (x % bandQ) (little endian)
+    int64_t offBVals;           // group base of the scores
+    int64_t offBTrace;          // group base of the trace
     int64_t offU;               // region U (c - r > dHi): TH[lb + 1], TS[lb + 1], M[lb + 1]
     int64_t offL;               // region L (c - r < dLo): TV[la + 1], TS[la + 1], M[la + 1]
 };
@@ -139,9 +145,16 @@ struct PairOutHdr
 // DP fill over the pairs listed in pairIdx[0..n) that all have the same R.
 cudaError_t launch_gotoh_fill(int R, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t const * negBuf, int32_t go, int32_t ge, cudaStream_t stream);
-// band DP fill (kernels_band.cu) over the pairs listed in pairIdx[0..n) that all have bandL == L (16 or 32)
-cudaError_t launch_gotoh_band(int L, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
+// band DP fill (kernels_band.cu) over warp groups of 32 / G pairs with the same band shape (G lanes per pair, blocks
+// of Q diagonals): pairIdx[0..nSlots) lists the groups slot by slot, -1 = empty slot
+cudaError_t launch_gotoh_band(int G, int Q, int nSlots, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t go, int32_t ge, cudaStream_t stream);
+bool band_shape_supported(int G, int Q);
+// position (in ints, relative to offBVals) of the score of band cell (row r, diagonal index x)
+__host__ __device__ inline int64_t band_val_index(int bandW, int ppw, int slot, int r, int x)
+{
+    return (((int64_t)r * (bandW >> 2) + (x >> 2)) * ppw + slot) * 4 + (x & 3);
+}
 // traceback + valid_solution + matching + bounds + update for all n pairs of the batch
 cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                 DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,

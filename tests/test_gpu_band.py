@@ -1,5 +1,6 @@
 """GPU parity tests of the BAND kernels through the C ABI (-m gpu): banded fill + closed-form regions + traceback
-against the oracle's full-matrix Gotoh on identical inputs.  Bit-exact scores, lines and gap scores."""
+against the oracle's full-matrix Gotoh on identical inputs.  Bit-exact scores, lines and gap scores.
+Band shapes: width W diagonals, G lanes per problem, blocks of Q = W / (2 G) diagonals (16 or 4)."""
 import numpy as np
 import pytest
 
@@ -9,6 +10,9 @@ pytestmark = pytest.mark.gpu
 
 GO, GE = -49152, -16384
 INIT = -1431655764
+
+# (band width, lanes per problem)
+SHAPES = [(32, 1), (64, 2), (128, 4), (256, 8), (512, 16), (1024, 32), (32, 4), (64, 8), (128, 16), (256, 32)]
 
 
 def band_pssm(rng, n, la, lb, d_lo, d_hi, density, alphabet=None):
@@ -25,9 +29,9 @@ def band_pssm(rng, n, la, lb, d_lo, d_hi, density, alphabet=None):
     return p
 
 
-def check(ctx, pssm, d_lo, lanes, go=GO, ge=GE):
+def check(ctx, pssm, d_lo, width, lanes, go=GO, ge=GE):
     from oracle import binding as ob
-    score, nl, la_, lb_, gap = ctx.gotoh_band_batch(pssm, d_lo, lanes, go, ge)
+    score, nl, la_, lb_, gap = ctx.gotoh_band_batch(pssm, d_lo, width, lanes, go, ge)
     for i in range(pssm.shape[0]):
         s, a, b, g = ob.gotoh(pssm[i], go, ge)
         assert score[i] == s, "problem %d: score %d vs %d" % (i, score[i], s)
@@ -36,45 +40,63 @@ def check(ctx, pssm, d_lo, lanes, go=GO, ge=GE):
         assert gap[i] == g
 
 
-@pytest.mark.parametrize("la,lb,d_lo,lanes", [
-    (1, 1, 0, 16), (2, 1, 0, 16), (7, 5, -2, 16), (40, 33, -8, 16), (64, 64, -16, 16), (150, 150, -12, 16),
-    (300, 300, -14, 16), (300, 290, -10, 16), (97, 65, -20, 32), (300, 300, -30, 32), (330, 257, -6, 32),
-    (600, 600, -32, 32)])
-def test_band_random(gpu_ctx_factory, la, lb, d_lo, lanes):
+@pytest.mark.parametrize("width,lanes", SHAPES)
+@pytest.mark.parametrize("la,lb,frac", [(1, 1, 0.0), (2, 1, 0.0), (7, 5, 0.3), (40, 33, 0.5), (64, 64, 0.5), (150, 150, 0.4),
+                                        (300, 300, 0.45), (300, 290, 0.3), (330, 257, 0.2)])
+def test_band_random(gpu_ctx_factory, la, lb, frac, width, lanes):
+    """frac: share of the band below the main diagonal (d_lo = -frac * width)."""
     ctx, _ = gpu_ctx_factory()
-    rng = np.random.default_rng(la * 977 + lb + lanes)
-    d_hi = d_lo + 2 * lanes - 1
+    rng = np.random.default_rng(la * 977 + lb + width + lanes)
+    d_lo = -int(frac * width)
+    d_hi = d_lo + width - 1
+    # more problems than one warp group holds (32 / lanes), so that slots and partial groups are covered
+    n = 5 if lanes > 8 else 37
+    if la * lb * n > 4e6:
+        n = max(3, int(4e6 // (la * lb)))
     for density in (0.15, 0.6):
-        check(ctx, band_pssm(rng, 5, la, lb, d_lo, d_hi, density), d_lo, lanes)
+        check(ctx, band_pssm(rng, n, la, lb, d_lo, d_hi, density), d_lo, width, lanes)
 
 
-@pytest.mark.parametrize("la,lb,d_lo,lanes", [(12, 12, -4, 16), (70, 50, -10, 16), (150, 140, -8, 16), (90, 90, -20, 32)])
-def test_band_ties(gpu_ctx_factory, la, lb, d_lo, lanes):
+@pytest.mark.parametrize("width,lanes", [(32, 1), (32, 4), (64, 2), (64, 8)])
+@pytest.mark.parametrize("la,lb,d_lo", [(12, 12, -4), (70, 50, -10), (150, 140, -8), (90, 90, -20)])
+def test_band_ties(gpu_ctx_factory, la, lb, d_lo, width, lanes):
     """Small score alphabet: masses of ties, inside the band and against the closed-form regions."""
     ctx, _ = gpu_ctx_factory()
     rng = np.random.default_rng(5 + la)
-    d_hi = d_lo + 2 * lanes - 1
+    d_hi = d_lo + width - 1
     alpha = (np.array([-2, -1, 0, 1, 2]) * 16384).astype(np.int64)
     p = band_pssm(rng, 8, la, lb, d_lo, d_hi, 0.5, alpha)
-    check(ctx, p, d_lo, lanes)
-    check(ctx, p, d_lo, lanes, go=-3 * 8192, ge=-1 * 8192)
+    check(ctx, p, d_lo, width, lanes)
+    check(ctx, p, d_lo, width, lanes, go=-3 * 8192, ge=-1 * 8192)
 
 
-@pytest.mark.parametrize("la,lb,d_lo,lanes", [(200, 60, 0, 16), (200, 60, -6, 16), (400, 100, -2, 32), (120, 119, 0, 16)])
-def test_band_end_cell_outside_and_escapes(gpu_ctx_factory, la, lb, d_lo, lanes):
+@pytest.mark.parametrize("width,lanes", [(32, 1), (32, 4), (64, 2), (64, 8)])
+@pytest.mark.parametrize("la,lb,d_lo", [(200, 60, 0), (200, 60, -6), (400, 100, -2), (120, 119, 0), (90, 80, -31)])
+def test_band_end_cell_outside_and_escapes(gpu_ctx_factory, la, lb, d_lo, width, lanes):
     """la - lb beyond the band: the end cell and the start of the traceback lie in region U; d_lo = 0 pushes
-    vertical detours into region L."""
+    vertical detours into region L; d_lo = -31 puts the main diagonal at the band's upper edge."""
     ctx, _ = gpu_ctx_factory()
     rng = np.random.default_rng(la + 3 * lb + d_lo)
-    d_hi = d_lo + 2 * lanes - 1
+    d_hi = d_lo + width - 1
     for density in (0.05, 0.3, 0.9):
-        check(ctx, band_pssm(rng, 6, la, lb, d_lo, d_hi, density), d_lo, lanes)
+        check(ctx, band_pssm(rng, 6, la, lb, d_lo, d_hi, density), d_lo, width, lanes)
+
+
+def test_band_long(gpu_ctx_factory):
+    """Longer than the single-pass full-matrix kernel allows (lenB > 640)."""
+    ctx, _ = gpu_ctx_factory()
+    rng = np.random.default_rng(77)
+    la, lb, d_lo, width = 1000, 900, -40, 256
+    p = band_pssm(rng, 3, la, lb, d_lo, d_lo + width - 1, 0.3)
+    check(ctx, p, d_lo, width, 8)
+    check(ctx, p, d_lo, width, 32)
 
 
 def test_band_all_inactive(gpu_ctx_factory):
     ctx, _ = gpu_ctx_factory()
     p = np.full((2, 50, 37), INIT, np.int32)
-    check(ctx, p, -4, 16)
+    check(ctx, p, -4, 32, 1)
+    check(ctx, p, -4, 32, 4)
 
 
 def test_band_rejects_active_cell_outside(gpu_ctx_factory):
@@ -83,4 +105,4 @@ def test_band_rejects_active_cell_outside(gpu_ctx_factory):
     p = np.full((1, 80, 80), INIT, np.int32)
     p[0, 70, 2] = 100
     with pytest.raises(lb.LaraError):
-        ctx.gotoh_band_batch(p, -4, 16, GO, GE)
+        ctx.gotoh_band_batch(p, -4, 32, 1, GO, GE)
