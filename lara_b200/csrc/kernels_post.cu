@@ -651,14 +651,10 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         return;
     }
 
-    int32_t const * __restrict__ seqScore = arena + d.offSeqScore;
-    int32_t * __restrict__ pv = arena + d.offPv;
-    int32_t const * __restrict__ ioff = arena + d.offIoff;
-    int32_t const * __restrict__ part = arena + d.offPart;
-    int32_t const * __restrict__ ppos = arena + d.offPpos;
-    int32_t const * __restrict__ sc = arena + d.offSc;
-    int32_t * __restrict__ dual = arena + d.offDual;
-    int32_t const * __restrict__ rev = arena + d.offRev;
+    // per edge { seqScore, pv, ioff, degree }, per interaction { partner, partner cell, structScore, dual } and
+    // { reverse index, seqScore of the partner, owner, 0 }  (lara_gpu.cuh: offEdge, offInter)
+    int4 * __restrict__ edge = reinterpret_cast<int4 *>(arena + d.offEdge);
+    int4 * __restrict__ inter = reinterpret_cast<int4 *>(arena + d.offInter);
     int32_t * __restrict__ list = arena + d.offList;
     // candidates are collected in shared memory when their upper bound fits, else in the pair's global buffer
     // (and moved to shared memory for the sort when the actual number fits)
@@ -684,22 +680,24 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     {
         int const e = sm.curE[i];
         if (e < 0) continue;
-        int32_t const sq = seqScore[e];
-        int32_t const top = pv[e];
+        int4 const er = edge[e];
+        int32_t const sq = er.x, top = er.y;
         lbSeq += sq;
-        for (int x = ioff[e]; x < ioff[e + 1]; ++x)
+        for (int x = er.z; x < er.z + er.w; ++x)
         {
-            int const m = part[x];
-            uint32_t const pp = (uint32_t)ppos[x];
+            int4 const r0 = inter[2 * (size_t)x];
+            int const m = r0.x;
+            uint32_t const pp = (uint32_t)r0.y;
+            int32_t const s = r0.z;
             int const li = sm.lineOfA[pp >> 16];
             bool const inSol = li >= 0 && (sm.linesRev[nLines - 1 - li] & 0xffffu) == (pp & 0xffffu);
-            int32_t const s = sc[x];
-            if (sq + s + dual[x] == top)
+            if (sq + s + r0.w == top)
             {
+                int4 const r1 = inter[2 * (size_t)x + 1];
+                int const rx = r1.x;
                 bool cycle = false;
-                int const rx = rev[x];
                 if (inSol)
-                    cycle = (seqScore[m] + s + dual[rx] == pv[m]);
+                    cycle = (r1.y + s + inter[2 * (size_t)rx].w == edge[m].y);
                 if (!cycle)
                 {
                     int const at = atomicAdd(&sm.misc[0], 2);
@@ -746,19 +744,22 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         {
             int const e = sm.curE[i];
             if (e < 0) continue;
-            int32_t const sq = seqScore[e], top = pv[e];
+            int4 const er = edge[e];
+            int32_t const sq = er.x, top = er.y;
             int found = -1;
             bool selfFirst = false;
-            for (int x = ioff[e]; x < ioff[e + 1] && found < 0 && !selfFirst; ++x)
+            int4 rf = make_int4(0, 0, 0, 0);
+            for (int x = er.z; x < er.z + er.w && found < 0 && !selfFirst; ++x)
             {
-                if (part[x] > e && sq == top) { selfFirst = true; break; }
-                if (sq + sc[x] + dual[x] == top) found = x;
+                int4 const r0 = inter[2 * (size_t)x];
+                if (r0.x > e && sq == top) { selfFirst = true; break; }
+                if (sq + r0.z + r0.w == top) { found = x; rf = r0; }
             }
             if (found >= 0 && !selfFirst)
             {
-                add += sc[found];
+                add += rf.z;
                 sm.matched[i] = 1;
-                int const li = sm.lineOfA[(uint32_t)ppos[found] >> 16];
+                int const li = sm.lineOfA[(uint32_t)rf.y >> 16];
                 if (li >= 0) sm.matched[li] = 1;
             }
         }
@@ -818,9 +819,10 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     for (int i = lane; i < nList; i += 32)
     {
         uint32_t const x = (uint32_t)list[i];
-        int const di = (int)(x & 0x7fffffffu);
-        float const f = __int2float_rn(dual[di]);
-        dual[di] = __float2int_rz((x >> 31) ? __fadd_rn(f, stepSize) : __fsub_rn(f, stepSize));
+        size_t const di = (size_t)(x & 0x7fffffffu);
+        int32_t * const dual = &reinterpret_cast<int32_t *>(inter + 2 * di)[3];
+        float const f = __int2float_rn(*dual);
+        *dual = __float2int_rz((x >> 31) ? __fadd_rn(f, stepSize) : __fsub_rn(f, stepSize));
     }
     __syncwarp();
 
@@ -831,13 +833,17 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         int32_t const * __restrict__ perm = arena + d.offPerm;
         for (int i = lane; i < nList; i += 32)
         {
-            int const di = (int)((uint32_t)list[i] & 0x7fffffffu);
-            int const l = part[rev[di]];                    // owner of interaction di
-            int32_t const sq = seqScore[l];
+            size_t const di = (size_t)((uint32_t)list[i] & 0x7fffffffu);
+            int const l = inter[2 * di + 1].z;              // owner of interaction di
+            int4 const er = edge[l];
+            int32_t const sq = er.x;
             int32_t top = sq;
-            for (int x = ioff[l]; x < ioff[l + 1]; ++x)
-                top = max(top, sq + sc[x] + dual[x]);
-            pv[l] = top;
+            for (int x = er.z; x < er.z + er.w; ++x)
+            {
+                int4 const r0 = inter[2 * (size_t)x];
+                top = max(top, sq + r0.z + r0.w);
+            }
+            reinterpret_cast<int32_t *>(edge + l)[1] = top;
             vals[perm[l]] = top;
         }
         return;
@@ -852,7 +858,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     {
         // minmax over ALL lenA*lenB queues (:445-448); an inactive edge's empty std::set reads as 0 there
         int32_t mn = INT32_MAX, mx = INT32_MIN;
-        for (int e = lane; e < d.E; e += 32) { mn = min(mn, pv[e]); mx = max(mx, pv[e]); }
+        for (int e = lane; e < d.E; e += 32) { int32_t const t = edge[e].y; mn = min(mn, t); mx = max(mx, t); }
         if ((int64_t)d.E < (int64_t)d.la * d.lb) { mn = min(mn, 0); mx = max(mx, 0); }
         minScore = warp_min(mn);
         maxScore = warp_max(mx);
@@ -869,7 +875,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         if (P.libLinear)
         {
             int const e = edge_of(d, arena, a, b);
-            unsigned long long const prod = (unsigned long long)isMatched * (unsigned long long)(long long)(pv[e] - minScore);
+            unsigned long long const prod = (unsigned long long)isMatched * (unsigned long long)(long long)(edge[e].y - minScore);
             int32_t const val = __float2int_rz(__fmul_rn(__ull2float_rn(prod), div));
             w = P.libMin + (uint32_t)val;
         }

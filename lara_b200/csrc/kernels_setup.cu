@@ -431,7 +431,24 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
         ptr += R;
     }
     }
-    // 4. solver state (src/subgradient_solver.hpp:86-100, simd :153,387-393)
+    // 4. records of the iteration kernel (lara_gpu.cuh: offEdge, offInter)
+    __syncwarp();
+    {
+        int4 * __restrict__ edge = reinterpret_cast<int4 *>(arena + d.offEdge);
+        int4 * __restrict__ inter = reinterpret_cast<int4 *>(arena + d.offInter);
+        for (int e = lane; e < E; e += 32)
+        {
+            int const x0 = ioff[e], x1 = ioff[e + 1];
+            edge[e] = make_int4(seqScore[e], pv[e], x0, x1 - x0);
+            for (int x = x0; x < x1; ++x)
+            {
+                int const m = part[x];
+                inter[2 * (size_t)x] = make_int4(m, ppos[x], sc[x], 0);
+                inter[2 * (size_t)x + 1] = make_int4(rev[x], seqScore[m], e, 0);
+            }
+        }
+    }
+    // 5. solver state (src/subgradient_solver.hpp:86-100, simd :153,387-393)
     if (lane == 0)
     {
         PairState & st = state[p];

@@ -331,7 +331,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     for (int i = 0; i < n; ++i)
     {
         PairDesc & d = desc[(size_t)i];
-        sizeB += 4 * align4(std::max(d.E, 1)) + align4(d.E + 1);
+        sizeB += 8 * align4(std::max(d.E, 1)) + align4(d.E + 1);
         if (d.bandW > 0)
             sizeB += align4(3ll * (d.lb + 1)) + align4(3ll * (d.la + 1));
         else
@@ -353,6 +353,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         PairDesc & d = desc[(size_t)i];
         d.offCell = rB.take(d.E); d.offSeqScore = rB.take(d.E); d.offPv = rB.take(d.E); d.offPerm = rB.take(d.E);
         d.offIoff = rB.take(d.E + 1);
+        d.offEdge = rB.take(4ll * d.E);
         if (d.bandW > 0)
         {
             d.offU = rB.take(3ll * (d.lb + 1));
@@ -385,7 +386,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     CK(cudaStreamSynchronize(s));
     wk.stats.kernel_launches += 1;
     int64_t sizeC = 0;
-    for (int i = 0; i < n; ++i) sizeC += 6 * align4(std::max(desc[(size_t)i].D, 1)) + align4(std::max(desc[(size_t)i].nVals, 1));
+    for (int i = 0; i < n; ++i) sizeC += 14 * align4(std::max(desc[(size_t)i].D, 1)) + 8 + align4(std::max(desc[(size_t)i].nVals, 1));
     Region rC;
     CK(cudaMallocAsync((void **)&rC.ptr, (size_t)sizeC * 4, s));
     rC.size = sizeC; rC.baseDelta = rC.ptr - arena;
@@ -394,6 +395,8 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         PairDesc & d = desc[(size_t)i];
         d.offPart = rC.take(d.D); d.offPpos = rC.take(d.D); d.offSc = rC.take(d.D); d.offDual = rC.take(d.D);
         d.offRev = rC.take(d.D); d.offList = rC.take(d.D); d.offVals = rC.take(d.nVals);
+        rC.used = (rC.used + 7) & ~(int64_t)7;            // 32-byte records
+        d.offInter = rC.take(8ll * d.D);
         wk.stats.n_active_edges += d.E; wk.stats.n_interactions += d.D;
         wk.stats.filter_cells += 2ll * d.la * d.lb;
     }

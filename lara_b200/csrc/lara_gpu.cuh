@@ -73,6 +73,11 @@ struct PairDesc
     int64_t offDual;            // per interaction: Lagrange multiplier [D]
     int64_t offRev;             // per interaction: index of the reverse interaction [D]
     int64_t offList;            // subgradient index list (sign in bit 31) [D]
+    // records read by the iteration kernel (written at the end of the set-up from the arrays above, which stay
+    // as the build-time form; pv and dual live only here afterwards):
+    int64_t offEdge;            // per edge, 16 bytes: { seqScore, pv (queue top == pssm value), ioff, degree }   [E]
+    int64_t offInter;           // per interaction, 32 bytes: { partner edge, partner cell, structScore, dual,
+                                //                               reverse index, seqScore of the partner, owner edge, 0 }  [D]
     int64_t offLines;           // current lines  (a << 16) | b  [lb]
     int64_t offBest;            // best lines     (a << 16) | b | matched << 31  [lb]
     int64_t offCand;            // global candidate buffer for the matching sort, 2 words each [2 * kCap] (8-byte aligned)
