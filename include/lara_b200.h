@@ -186,8 +186,8 @@ int lara_gpu_gotoh_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32
  * The same alignment computed by the BAND kernels (lara_b200/csrc/kernels_band.cu): only the diagonals
  * d_lo <= a - b <= d_lo + band_width - 1 are filled (d_lo <= 0 <= d_lo + band_width - 1), the rest of the matrix is
  * covered by closed forms.  `lanes` threads work on one problem, each on two blocks of band_width / (2 * lanes)
- * diagonals; supported: blocks of 16 diagonals with 1, 2, 4, 8, 16 or 32 lanes (band_width 32 .. 1024) and blocks of
- * 4 diagonals with 4, 8, 16 or 32 lanes (band_width 32 .. 256).  Every active cell (pssm > -2^30) must lie inside the
+ * diagonals; supported: blocks of 16 diagonals with 1, 2, 4, 8, 16 or 32 lanes (band_width 32 .. 1024), blocks of 8
+ * with 2 .. 32 lanes (band_width 32 .. 512) and blocks of 4 with 4 .. 32 lanes (band_width 32 .. 256).  Every active cell (pssm > -2^30) must lie inside the
  * band; the result is then identical to lara_gpu_gotoh_batch.  Needs gap_open < gap_extend.
  */
 int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, int32_t lenB,

@@ -131,8 +131,9 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
 
     int4 const * __restrict__ vals = reinterpret_cast<int4 const *>(arena + d.offBVals) + q;
     void * const trace = arena + d.offBTrace;
-    int32_t * __restrict__ uTH = arena + d.offU, * uTS = uTH + (lb + 1), * uM = uTS + (lb + 1);
-    int32_t * __restrict__ lTV = arena + d.offL, * lTS = lTV + (la + 1), * lM = lTS + (la + 1);
+    // closed-form records of the gap regions, interleaved over the pairs of the group: U per row, L per column
+    int4 * __restrict__ uRec = reinterpret_cast<int4 *>(arena + d.offU) + q;      // { TH, TS, M, 0 } at [r * PPW]
+    int4 * __restrict__ lRec = reinterpret_cast<int4 *>(arena + d.offL) + q;      // { TV, TS, M, 0 } at [c * PPW]
 
     // end cell (la, lb): block and diagonal inside the block, if it lies in the band
     int const idxEnd = la - lb - dLo;
@@ -195,7 +196,7 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
                     int32_t const vl = max(tv, ts);                              // first L cell of column c-1
                     hL = (c - 1 >= 1) ? (c + r - 2) * ge + go + runL : kBandNeg;
                     sL = max(vl, hL);
-                    lTV[c - 1] = tv - r * ge; lTS[c - 1] = ts - r * ge; lM[c - 1] = runL;
+                    lRec[(size_t)(c - 1) * PPW] = make_int4(tv - r * ge, ts - r * ge, runL, 0);
                     runL = max(runL, vl - r * ge - (c - 1) * ge);
                 }
             }
@@ -228,7 +229,7 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
                     int32_t const hu = max(th, ts);                              // first U cell of row r-1
                     vU = (r - 1 >= 1) ? (c + r - 2) * ge + go + runU : kBandNeg;
                     sU = max(vU, hu);
-                    uTH[r - 1] = th - c * ge; uTS[r - 1] = ts - c * ge; uM[r - 1] = runU;
+                    uRec[(size_t)(r - 1) * PPW] = make_int4(th - c * ge, ts - c * ge, runU, 0);
                     runU = max(runU, hu - c * ge - (r - 1) * ge);
                 }
             }
@@ -267,6 +268,7 @@ cudaError_t launch_gq(int nSlots, int32_t const * pairIdx, PairDesc const * desc
 bool band_shape_supported(int G, int Q)
 {
     if (Q == 16) return G == 1 || G == 2 || G == 4 || G == 8 || G == 16 || G == 32;
+    if (Q == 8) return G == 2 || G == 4 || G == 8 || G == 16 || G == 32;
     if (Q == 4) return G == 4 || G == 8 || G == 16 || G == 32;
     return false;
 }
@@ -278,6 +280,7 @@ cudaError_t launch_gotoh_band(int G, int Q, int nSlots, int32_t const * pairIdx,
         return cudaSuccess;
 #define LARA_GQ(g_, q_) if (G == g_ && Q == q_) return launch_gq<g_, q_>(nSlots, pairIdx, desc, state, arena, go, ge, stream);
     LARA_GQ(1, 16) LARA_GQ(2, 16) LARA_GQ(4, 16) LARA_GQ(8, 16) LARA_GQ(16, 16) LARA_GQ(32, 16)
+    LARA_GQ(2, 8) LARA_GQ(4, 8) LARA_GQ(8, 8) LARA_GQ(16, 8) LARA_GQ(32, 8)
     LARA_GQ(4, 4) LARA_GQ(8, 4) LARA_GQ(16, 4) LARA_GQ(32, 4)
 #undef LARA_GQ
     return cudaErrorInvalidValue;

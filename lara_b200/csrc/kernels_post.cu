@@ -239,29 +239,31 @@ struct BandView
     int W, Q, ppw, slot;                    // band geometry and position in the warp group (lara_gpu.cuh: PairDesc)
     int32_t go, ge;
     uint16_t const * trace;                 // group base of the trace, in half words (4 nibbles each)
-    int32_t const * uTH, * uTS, * uM;      // per row
-    int32_t const * lTV, * lTS, * lM;      // per column
+    int4 const * uRec;                      // per row    { TH, TS, M, 0 } at [r * ppw]   (already offset by the slot)
+    int4 const * lRec;                      // per column { TV, TS, M, 0 } at [c * ppw]
 };
 
-__device__ __forceinline__ int32_t band_uV(BandView const & v, int c, int r)
+__device__ __forceinline__ int4 band_u(BandView const & v, int r) { return __ldg(v.uRec + (size_t)r * v.ppw); }
+__device__ __forceinline__ int4 band_l(BandView const & v, int c) { return __ldg(v.lRec + (size_t)c * v.ppw); }
+__device__ __forceinline__ int32_t band_uV(BandView const & v, int4 const & u, int c, int r)
 {
-    return r == 0 ? kBandNeg : (c + r - 1) * v.ge + v.go + v.uM[r];
+    return r == 0 ? kBandNeg : (c + r - 1) * v.ge + v.go + u.z;
 }
-__device__ __forceinline__ int32_t band_uH(BandView const & v, int c, int r)
+__device__ __forceinline__ int32_t band_uH(BandView const & v, int4 const & u, int c, int r)
 {
-    int32_t const t = max(v.uTH[r], v.uTS[r]);
+    int32_t const t = max(u.x, u.y);
     bool const first = (c == r + v.dHi + 1) || r == 0;
-    return c * v.ge + (first ? t : max(t, v.uM[r] + 2 * v.go + (r - 2) * v.ge));
+    return c * v.ge + (first ? t : max(t, u.z + 2 * v.go + (r - 2) * v.ge));
 }
-__device__ __forceinline__ int32_t band_lH(BandView const & v, int c, int r)
+__device__ __forceinline__ int32_t band_lH(BandView const & v, int4 const & l, int c, int r)
 {
-    return c == 0 ? kBandNeg : (c + r - 1) * v.ge + v.go + v.lM[c];
+    return c == 0 ? kBandNeg : (c + r - 1) * v.ge + v.go + l.z;
 }
-__device__ __forceinline__ int32_t band_lV(BandView const & v, int c, int r)
+__device__ __forceinline__ int32_t band_lV(BandView const & v, int4 const & l, int c, int r)
 {
-    int32_t const t = max(v.lTV[c], v.lTS[c]);
+    int32_t const t = max(l.x, l.y);
     bool const first = (r == c - v.dLo + 1) || c == 0;
-    return r * v.ge + (first ? t : max(t, v.lM[c] + 2 * v.go + (c - 2) * v.ge));
+    return r * v.ge + (first ? t : max(t, l.z + 2 * v.go + (c - 2) * v.ge));
 }
 // nibble of a cell outside the band (c >= 1, r >= 1): the diagonal never wins there
 __device__ uint32_t band_outside_nib(BandView const & v, int c, int r)
@@ -269,27 +271,29 @@ __device__ uint32_t band_outside_nib(BandView const & v, int c, int r)
     uint32_t nib = kTrGap;
     if (c - r > v.dHi)
     {
-        int32_t const hCur = band_uH(v, c, r), vCur = band_uV(v, c, r);
-        if (c == r + v.dHi + 1) { if (v.uTH[r] < v.uTS[r]) nib |= kTrHOpen; }
+        int4 const u = band_u(v, r), up = band_u(v, r - 1);
+        int32_t const hCur = band_uH(v, u, c, r), vCur = band_uV(v, u, c, r);
+        if (c == r + v.dHi + 1) { if (u.x < u.y) nib |= kTrHOpen; }
         else
         {
-            int32_t const hl = band_uH(v, c - 1, r), vl = band_uV(v, c - 1, r);
+            int32_t const hl = band_uH(v, u, c - 1, r), vl = band_uV(v, u, c - 1, r);
             if (hl + v.ge < max(hl, vl) + v.go) nib |= kTrHOpen;
         }
-        int32_t const hu = band_uH(v, c, r - 1), vu = band_uV(v, c, r - 1);
+        int32_t const hu = band_uH(v, up, c, r - 1), vu = band_uV(v, up, c, r - 1);
         if (vu + v.ge < max(hu, vu) + v.go) nib |= kTrVOpen;
         if (vCur < hCur) nib |= kTrFromH;
     }
     else
     {
-        int32_t const hCur = band_lH(v, c, r), vCur = band_lV(v, c, r);
-        if (r == c - v.dLo + 1) { if (v.lTV[c] < v.lTS[c]) nib |= kTrVOpen; }
+        int4 const l = band_l(v, c), lp = band_l(v, c - 1);
+        int32_t const hCur = band_lH(v, l, c, r), vCur = band_lV(v, l, c, r);
+        if (r == c - v.dLo + 1) { if (l.x < l.y) nib |= kTrVOpen; }
         else
         {
-            int32_t const hu = band_lH(v, c, r - 1), vu = band_lV(v, c, r - 1);
+            int32_t const hu = band_lH(v, l, c, r - 1), vu = band_lV(v, l, c, r - 1);
             if (vu + v.ge < max(hu, vu) + v.go) nib |= kTrVOpen;
         }
-        int32_t const hl = band_lH(v, c - 1, r), vl = band_lV(v, c - 1, r);
+        int32_t const hl = band_lH(v, lp, c - 1, r), vl = band_lV(v, lp, c - 1, r);
         if (hl + v.ge < max(hl, vl) + v.go) nib |= kTrHOpen;
         if (vCur < hCur) nib |= kTrFromH;
     }
@@ -300,8 +304,8 @@ __device__ uint32_t band_outside_nib(BandView const & v, int c, int r)
 __device__ void band_end_values(BandView const & v, int32_t & sE, int32_t & vE, int32_t & hE)
 {
     int const c = v.la, r = v.lb;
-    if (c - r > v.dHi) { vE = band_uV(v, c, r); hE = band_uH(v, c, r); }
-    else { vE = band_lV(v, c, r); hE = band_lH(v, c, r); }
+    if (c - r > v.dHi) { int4 const u = band_u(v, r); vE = band_uV(v, u, c, r); hE = band_uH(v, u, c, r); }
+    else { int4 const l = band_l(v, c); vE = band_lV(v, l, c, r); hE = band_lH(v, l, c, r); }
     sE = max(vE, hE);
 }
 
@@ -344,6 +348,14 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
                     uint2 const u0 = __ldg(src), u1 = __ldg(src + v.ppw);
                     w[0] = u0.x; w[1] = u0.y; w[2] = u1.x; w[3] = u1.y;
                 }
+                else if (v.Q == 8)
+                {
+                    // units of 8 nibbles (one word)
+                    uint32_t const * __restrict__ src = reinterpret_cast<uint32_t const *>(v.trace) +
+                                                        ((size_t)rr * nUnits + (xLo >> 3)) * v.ppw + v.slot;
+                    #pragma unroll
+                    for (int h = 0; h < 4; ++h) w[h] = __ldg(src + (size_t)h * v.ppw);
+                }
                 else
                 {
                     // units of 4 nibbles (one half word)
@@ -357,12 +369,18 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
         }
         __syncwarp();
         // known(ci, ri): the trace decision of that cell can be evaluated now
-        auto fetch = [&](int ci, int ri, bool & known) -> uint32_t
+        // outside: the cell lies in a closed-form region and was not evaluated (lazy == true)
+        auto fetch = [&](int ci, int ri, bool & known, bool & outside, bool lazy) -> uint32_t
         {
-            known = false;
+            known = false; outside = false;
             if (ci < 1 || ri < 1) return 0u;
             int const dd = ci - ri;
-            if (dd > v.dHi || dd < v.dLo) { known = true; return band_outside_nib(v, ci, ri); }
+            if (dd > v.dHi || dd < v.dLo)
+            {
+                if (lazy) { outside = true; return 0u; }
+                known = true;
+                return band_outside_nib(v, ci, ri);
+            }
             int const x = dd - v.dLo - xLo, row = rHi - ri;
             if (row > 31 || x < 0 || x > 31) return 0u;
             known = true;
@@ -377,8 +395,8 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             }
             if (state == 0)
             {
-                bool known;
-                uint32_t nib = fetch(c - lane, r - lane, known);
+                bool known, outside;
+                uint32_t nib = fetch(c - lane, r - lane, known, outside, false);   // one diagonal: all in or all out
                 if (first && lane == 0)
                 {
                     if (endFix == 1) nib = (nib | kTrGap) & ~kTrFromH;
@@ -399,11 +417,19 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             }
             if (state == 1)
             {
-                bool known;
-                uint32_t const nib = fetch(c, r - lane, known);
-                unsigned const knownMask = __ballot_sync(kFull, known);
-                unsigned const extMask = __ballot_sync(kFull, known && !(nib & kTrVOpen) && (r - lane) != 1);
-                int const m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                // closed-form cells (beyond the band) are only evaluated when the run reaches them
+                bool known, outside;
+                uint32_t nib = fetch(c, r - lane, known, outside, true);
+                unsigned knownMask = __ballot_sync(kFull, known);
+                unsigned extMask = __ballot_sync(kFull, known && !(nib & kTrVOpen) && (r - lane) != 1);
+                int m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                if (m < 32 && ((__ballot_sync(kFull, outside) >> m) & 1u))
+                {
+                    if (outside) { nib = band_outside_nib(v, c, r - lane); known = true; }
+                    knownMask = __ballot_sync(kFull, known);
+                    extMask = __ballot_sync(kFull, known && !(nib & kTrVOpen) && (r - lane) != 1);
+                    m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                }
                 bool const closes = m < 32 && ((knownMask >> m) & 1u);
                 int const steps = closes ? m + 1 : m;
                 if (steps > 0)
@@ -417,11 +443,18 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             }
             else
             {
-                bool known;
-                uint32_t const nib = fetch(c - lane, r, known);
-                unsigned const knownMask = __ballot_sync(kFull, known);
-                unsigned const extMask = __ballot_sync(kFull, known && !(nib & kTrHOpen) && (c - lane) != 1);
-                int const m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                bool known, outside;
+                uint32_t nib = fetch(c - lane, r, known, outside, true);
+                unsigned knownMask = __ballot_sync(kFull, known);
+                unsigned extMask = __ballot_sync(kFull, known && !(nib & kTrHOpen) && (c - lane) != 1);
+                int m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                if (m < 32 && ((__ballot_sync(kFull, outside) >> m) & 1u))
+                {
+                    if (outside) { nib = band_outside_nib(v, c - lane, r); known = true; }
+                    knownMask = __ballot_sync(kFull, known);
+                    extMask = __ballot_sync(kFull, known && !(nib & kTrHOpen) && (c - lane) != 1);
+                    m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
+                }
                 bool const closes = m < 32 && ((knownMask >> m) & 1u);
                 int const steps = closes ? m + 1 : m;
                 if (steps > 0)
@@ -623,8 +656,8 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         bv.la = d.la; bv.lb = d.lb; bv.dLo = d.dLo; bv.dHi = d.dHi; bv.go = P.go; bv.ge = P.ge;
         bv.W = d.bandW; bv.Q = d.bandQ; bv.ppw = 32 / d.bandG; bv.slot = d.bandSlot;
         bv.trace = reinterpret_cast<uint16_t const *>(arena + d.offBTrace);
-        bv.uTH = arena + d.offU; bv.uTS = bv.uTH + (d.lb + 1); bv.uM = bv.uTS + (d.lb + 1);
-        bv.lTV = arena + d.offL; bv.lTS = bv.lTV + (d.la + 1); bv.lM = bv.lTS + (d.la + 1);
+        bv.uRec = reinterpret_cast<int4 const *>(arena + d.offU) + d.bandSlot;
+        bv.lRec = reinterpret_cast<int4 const *>(arena + d.offL) + d.bandSlot;
         int32_t sE = st.sEnd, vE = st.vEnd, hE = st.hEnd;
         int const dEnd = d.la - d.lb;
         if (dEnd > d.dHi || dEnd < d.dLo)
@@ -675,42 +708,83 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     __syncwarp();
 
     // ---- 3. subgradient marks, sequence part of the lower bound, matching candidates (:343-391) ----
+    // 32 lines at a time: their interactions are numbered consecutively (prefix sum of the degrees) and dealt to
+    // the lanes, two per lane and round, so that the record loads of a round are all in flight together
     int32_t lbSeq = 0;
-    for (int i = lane; i < nLines; i += 32)
+    uint32_t * const sOff = sm.win;                                 // [33] first item of each of the 32 lines
+    for (int base = 0; base < nLines; base += 32)
     {
-        int const e = sm.curE[i];
-        if (e < 0) continue;
-        int4 const er = edge[e];
-        int32_t const sq = er.x, top = er.y;
-        lbSeq += sq;
-        for (int x = er.z; x < er.z + er.w; ++x)
+        int const i = base + lane;
+        int const e = i < nLines ? sm.curE[i] : -1;
+        int4 er = make_int4(0, 0, 0, 0);
+        if (e >= 0) er = edge[e];
+        lbSeq += er.x;
+        int off = er.w;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
         {
-            int4 const r0 = inter[2 * (size_t)x];
-            int const m = r0.x;
-            uint32_t const pp = (uint32_t)r0.y;
-            int32_t const s = r0.z;
-            int const li = sm.lineOfA[pp >> 16];
-            bool const inSol = li >= 0 && (sm.linesRev[nLines - 1 - li] & 0xffffu) == (pp & 0xffffu);
-            if (sq + s + r0.w == top)
+            int const y = __shfl_up_sync(kFull, off, o);
+            if (lane >= o) off += y;
+        }
+        int const total = __shfl_sync(kFull, off, 31);
+        off -= er.w;
+        __syncwarp();
+        sOff[lane] = (uint32_t)off;
+        if (lane == 0) sOff[32] = (uint32_t)total;
+        __syncwarp();
+        for (int t0 = 0; t0 < total; t0 += 64)
+        {
+            int4 r0[2];
+            int xs[2], es[2], is[2];
+            int32_t sqs[2], tops[2];
+            bool act[2];
+            #pragma unroll
+            for (int u = 0; u < 2; ++u)
             {
-                int4 const r1 = inter[2 * (size_t)x + 1];
-                int const rx = r1.x;
-                bool cycle = false;
-                if (inSol)
-                    cycle = (r1.y + s + inter[2 * (size_t)rx].w == edge[m].y);
-                if (!cycle)
-                {
-                    int const at = atomicAdd(&sm.misc[0], 2);
-                    list[at] = x;                                   // subgradient +1
-                    list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
-                }
+                int const t = t0 + 32 * u + lane;
+                act[u] = t < total;
+                int o = 0;                                      // owner: the last line that starts at or before item t
+                #pragma unroll
+                for (int step = 16; step > 0; step >>= 1)
+                    if (sOff[o + step] <= (uint32_t)t) o += step;
+                es[u] = __shfl_sync(kFull, e, o);
+                sqs[u] = __shfl_sync(kFull, er.x, o);
+                tops[u] = __shfl_sync(kFull, er.y, o);
+                xs[u] = __shfl_sync(kFull, er.z, o) + (t - __shfl_sync(kFull, off, o));
+                is[u] = base + o;
+                r0[u] = make_int4(0, 0, 0, 0);
+                if (act[u]) r0[u] = inter[2 * (size_t)xs[u]];
             }
-            if (inSol && e < m)
+            #pragma unroll
+            for (int u = 0; u < 2; ++u)
             {
-                int const at = atomicAdd(&sm.misc[1], 1);
-                unsigned long long const key =
-                    ((unsigned long long)(~((uint32_t)s ^ 0x80000000u)) << 32) | ((unsigned long long)i << 16) | (unsigned long long)li;
-                if (at < d.kCap) cand[at] = key; else sm.misc[11] = 2;
+                if (!act[u]) continue;
+                int const x = xs[u], m = r0[u].x;
+                uint32_t const pp = (uint32_t)r0[u].y;
+                int32_t const s = r0[u].z;
+                int const li = sm.lineOfA[pp >> 16];
+                bool const inSol = li >= 0 && (sm.linesRev[nLines - 1 - li] & 0xffffu) == (pp & 0xffffu);
+                if (sqs[u] + s + r0[u].w == tops[u])
+                {
+                    int4 const r1 = inter[2 * (size_t)x + 1];
+                    int const rx = r1.x;
+                    bool cycle = false;
+                    if (inSol)
+                        cycle = (r1.y + s + inter[2 * (size_t)rx].w == edge[m].y);
+                    if (!cycle)
+                    {
+                        int const at = atomicAdd(&sm.misc[0], 2);
+                        list[at] = x;                                   // subgradient +1
+                        list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
+                    }
+                }
+                if (inSol && es[u] < m)
+                {
+                    int const at = atomicAdd(&sm.misc[1], 1);
+                    unsigned long long const key = ((unsigned long long)(~((uint32_t)s ^ 0x80000000u)) << 32) |
+                                                   ((unsigned long long)is[u] << 16) | (unsigned long long)li;
+                    if (at < d.kCap) cand[at] = key; else sm.misc[11] = 2;
+                }
             }
         }
     }

@@ -207,8 +207,8 @@ void choose_band_shape(lara_ctx const & ctx, int W, int nPairs, int & G, int & Q
     int const g16 = W / 32, g4 = W / 8;
     int64_t const warps16 = ((int64_t)nPairs * g16 + 31) / 32;
     Q = (g4 > 32 || warps16 >= ctx.bandMinWarps) ? 16 : 4;
-    if (ctx.bandForceQ == 16 || (ctx.bandForceQ == 4 && g4 <= 32)) Q = ctx.bandForceQ;
-    G = Q == 16 ? g16 : g4;
+    if (ctx.bandForceQ == 16 || (ctx.bandForceQ == 8 && W <= 512) || (ctx.bandForceQ == 4 && g4 <= 32)) Q = ctx.bandForceQ;
+    G = W / (2 * Q);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -297,7 +297,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     }
     struct BandClass { int G, Q; std::vector<int32_t> slots; };    // slots: pair index or -1, 32 / G per warp group
     std::vector<BandClass> bandClasses;
-    struct BandGroup { int W, ppw, rows, first, count; int cls; };
+    struct BandGroup { int W, ppw, rows, cols, first, count; int cls; };
     std::vector<BandGroup> groups;
     for (auto & kv : byW)
     {
@@ -313,7 +313,9 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         for (size_t k = 0; k < members.size(); k += (size_t)ppw)
         {
             int const cnt = (int)std::min<size_t>((size_t)ppw, members.size() - k);
-            groups.push_back(BandGroup{W, ppw, desc[(size_t)members[k]].lb + 1, (int)bandClasses[(size_t)ci].slots.size(), cnt, ci});
+            int cols = 0;
+            for (int j = 0; j < cnt; ++j) cols = std::max(cols, desc[(size_t)members[k + (size_t)j]].la + 1);
+            groups.push_back(BandGroup{W, ppw, desc[(size_t)members[k]].lb + 1, cols, (int)bandClasses[(size_t)ci].slots.size(), cnt, ci});
             for (int j = 0; j < ppw; ++j)
             {
                 if (j < cnt)
@@ -332,9 +334,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     {
         PairDesc & d = desc[(size_t)i];
         sizeB += 8 * align4(std::max(d.E, 1)) + align4(d.E + 1);
-        if (d.bandW > 0)
-            sizeB += align4(3ll * (d.lb + 1)) + align4(3ll * (d.la + 1));
-        else
+        if (d.bandW == 0)
         {
             if (d.R > kMaxR)
                 throw std::runtime_error("a pair whose shorter sequence exceeds " + std::to_string(32 * kMaxR) +
@@ -344,7 +344,8 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         }
     }
     for (BandGroup const & g : groups)
-        sizeB += align4((int64_t)g.rows * g.W * g.ppw) + align4((int64_t)g.rows * (g.W / 8) * g.ppw);
+        sizeB += align4((int64_t)g.rows * g.W * g.ppw) + align4((int64_t)g.rows * (g.W / 8) * g.ppw) +
+                 4ll * g.ppw * (g.rows + g.cols);
     Region rB;
     CK(cudaMallocAsync((void **)&rB.ptr, (size_t)sizeB * 4, s));
     rB.size = sizeB; rB.baseDelta = rB.ptr - arena;
@@ -356,8 +357,6 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         d.offEdge = rB.take(4ll * d.E);
         if (d.bandW > 0)
         {
-            d.offU = rB.take(3ll * (d.lb + 1));
-            d.offL = rB.take(3ll * (d.la + 1));
             ++wk.stats.reserved[1];                     // pairs solved by the band kernels
             if (d.bandQ == 16) ++wk.stats.reserved[2];  // ... of those in blocks of 16 diagonals
             wk.stats.reserved[3] += d.bandW;            // sum of their band widths
@@ -373,10 +372,12 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     {
         int64_t const ov = rB.take((int64_t)g.rows * g.W * g.ppw);
         int64_t const ot = rB.take((int64_t)g.rows * (g.W / 8) * g.ppw);
+        int64_t const ou = rB.take(4ll * g.ppw * g.rows);
+        int64_t const ol = rB.take(4ll * g.ppw * g.cols);
         for (int j = 0; j < g.count; ++j)
         {
             PairDesc & d = desc[(size_t)bandClasses[(size_t)g.cls].slots[(size_t)(g.first + j)]];
-            d.offBVals = ov; d.offBTrace = ot;
+            d.offBVals = ov; d.offBTrace = ot; d.offU = ou; d.offL = ol;
         }
     }
     CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
@@ -1116,7 +1117,7 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
     if (!ctx || !pssm || n_problems < 1 || lenA < 1 || lenB < 1) return set_err(ctx, LARA_E_INVALID, "bad argument");
     int const G = lanes, W = band_width, Q = (G > 0 && W % (2 * G) == 0) ? W / (2 * G) : 0;
     if (!band_shape_supported(G, Q) || d_lo > 0 || d_lo + W - 1 < 0)
-        return set_err(ctx, LARA_E_INVALID, "band: width / (2 * lanes) must be 16 (lanes 1..32) or 4 (lanes 4..32), "
+        return set_err(ctx, LARA_E_INVALID, "band: width / (2 * lanes) must be 16 (lanes 1..32), 8 (lanes 2..32) or 4 (lanes 4..32), "
                                             "and d_lo <= 0 <= d_lo + width - 1");
     if (!(gap_open < gap_extend)) return set_err(ctx, LARA_E_UNSUPPORTED, "band kernel needs gap_open < gap_extend");
     Device & dv = ctx->devs[0];
@@ -1136,6 +1137,8 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
             {
                 int64_t const ov = rg.take((int64_t)(lenB + 1) * W * ppw);
                 int64_t const ot = rg.take((int64_t)(lenB + 1) * (W / 8) * ppw);
+                int64_t const ou = rg.take(4ll * ppw * (lenB + 1));
+                int64_t const ol = rg.take(4ll * ppw * (lenA + 1));
                 for (int j = 0; j < ppw && gi * ppw + j < n; ++j)
                 {
                     int const i = gi * ppw + j;
@@ -1143,8 +1146,7 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
                     std::memset(&d, 0, sizeof(d));
                     d.la = lenA; d.lb = lenB; d.bandW = W; d.bandG = G; d.bandQ = Q; d.bandSlot = j; d.dLo = d_lo; d.dHi = dHi;
                     d.offBVals = ov; d.offBTrace = ot;
-                    d.offU = rg.take(3ll * (lenB + 1));
-                    d.offL = rg.take(3ll * (lenA + 1));
+                    d.offU = ou; d.offL = ol;
                     d.offLines = rg.take(lenB);
                     slots[(size_t)i] = i;
                 }
