@@ -48,6 +48,7 @@ namespace
 {
 
 constexpr unsigned kFull = 0xffffffffu;
+constexpr int kPrefetchRows = 3;
 
 template <int Q> struct TraceUnit;
 template <> struct TraceUnit<4>  { using type = uint16_t; };
@@ -129,11 +130,13 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
     if (lbMax < 1)
         return;
 
-    int4 const * __restrict__ vals = reinterpret_cast<int4 const *>(arena + d.offBVals) + q;
+    // the pair's own slot in its group's interleaved arrays (== q until the slot list has been compacted)
+    int const gs = live ? d.bandSlot : 0;
+    int4 const * __restrict__ vals = reinterpret_cast<int4 const *>(arena + d.offBVals) + gs;
     void * const trace = arena + d.offBTrace;
     // closed-form records of the gap regions, interleaved over the pairs of the group: U per row, L per column
-    int4 * __restrict__ uRec = reinterpret_cast<int4 *>(arena + d.offU) + q;      // { TH, TS, M, 0 } at [r * PPW]
-    int4 * __restrict__ lRec = reinterpret_cast<int4 *>(arena + d.offL) + q;      // { TV, TS, M, 0 } at [c * PPW]
+    int4 * __restrict__ uRec = reinterpret_cast<int4 *>(arena + d.offU) + gs;      // { TH, TS, M, 0 } at [r * PPW]
+    int4 * __restrict__ lRec = reinterpret_cast<int4 *>(arena + d.offL) + gs;      // { TV, TS, M, 0 } at [c * PPW]
 
     // end cell (la, lb): block and diagonal inside the block, if it lies in the band
     int const idxEnd = la - lb - dLo;
@@ -180,6 +183,15 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
         int const r = i - g + 1;
         bool const rowValid = r >= 1 && r <= lb;
         if (rowValid) load_run(subB, r, 2 * g + 1);
+        // the register pipeline is half a row deep; under load HBM answers later than that, so the rows
+        // kPrefetchRows ahead are pulled into L2 meanwhile (a warp's 16-byte chunks of one row are contiguous)
+        if (r + kPrefetchRows <= lb && r + kPrefetchRows >= 1)
+        {
+            int4 const * __restrict__ src = vals + ((size_t)(r + kPrefetchRows) * NCH + (size_t)(2 * g) * CQ) * PPW;
+            #pragma unroll
+            for (int k = 0; k < 2 * CQ; ++k)
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(src + (size_t)k * PPW));
+        }
         // ------------------------------ block A ----------------------------------------------------------------
         {
             int32_t hL = __shfl_up_sync(kFull, HB, 1, G);
@@ -209,7 +221,7 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
                     HA = band_run<Q, true>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, tw, jEnd, sE, vE, hE);
                 else
                     HA = band_run<Q, false>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, tw, 0, sE, vE, hE);
-                store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g)) * PPW + q, tw);
+                store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g)) * PPW + gs, tw);
             }
         }
         if (r + 1 >= 1 && r + 1 <= lb) load_run(subA, r + 1, 2 * g);
@@ -242,7 +254,7 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
                     HB = band_run<Q, true>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, tw, jEnd, sE, vE, hE);
                 else
                     HB = band_run<Q, false>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, tw, 0, sE, vE, hE);
-                store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g + 1)) * PPW + q, tw);
+                store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g + 1)) * PPW + gs, tw);
             }
         }
     }
@@ -251,6 +263,42 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
         PairState & st = state[p];
         st.currentUpper = sE; st.sEnd = sE; st.vEnd = vE; st.hEnd = hE;
     }
+}
+
+// Dense list of the slots whose pair is still iterating, in the old order (stable: the pairs of a warp group that
+// all go on stay neighbours, so the DP's loads stay coalesced).  One block; n is a batch's slot count.
+__global__ void __launch_bounds__(1024)
+compact_slots_kernel(int n, int32_t const * __restrict__ in, PairState const * __restrict__ state,
+                     int32_t * __restrict__ out, int32_t * __restrict__ count)
+{
+    __shared__ int warpCount[32];
+    __shared__ int base;
+    int const tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) base = 0;
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += 1024)
+    {
+        int const i = i0 + tid;
+        int const p = i < n ? in[i] : -1;
+        bool const live = p >= 0 && state[p].done == 0;
+        unsigned const bal = __ballot_sync(kFull, live);
+        if (lane == 0) warpCount[w] = __popc(bal);
+        __syncthreads();
+        int before = 0, total = 0;
+        #pragma unroll
+        for (int k = 0; k < 32; ++k)
+        {
+            int const c = warpCount[k];
+            before += k < w ? c : 0;
+            total += c;
+        }
+        int const b = base;
+        if (live) out[b + before + __popc(bal & ((1u << lane) - 1u))] = p;
+        __syncthreads();
+        if (tid == 0) base = b + total;
+        __syncthreads();
+    }
+    if (tid == 0) *count = base;
 }
 
 template <int G, int Q>
@@ -264,6 +312,14 @@ cudaError_t launch_gq(int nSlots, int32_t const * pairIdx, PairDesc const * desc
 }
 
 } // namespace
+
+cudaError_t launch_compact_slots(int n, int32_t const * in, PairState const * state, int32_t * out, int32_t * count,
+                                 cudaStream_t stream)
+{
+    if (n <= 0) return cudaSuccess;
+    compact_slots_kernel<<<1, 1024, 0, stream>>>(n, in, state, out, count);
+    return cudaGetLastError();
+}
 
 bool band_shape_supported(int G, int Q)
 {

@@ -27,15 +27,19 @@ constexpr int kMaxLookahead = 8;
 __constant__ uint8_t cSlotX[28] = {0,0,0,0,0,0,0, 1,1,1,1,1,1, 2,2,2,2,2, 3,3,3,3, 4,4,4, 5,5, 6};
 __constant__ uint8_t cSlotY[28] = {1,2,3,4,5,6,7, 2,3,4,5,6,7, 3,4,5,6,7, 4,5,6,7, 5,6,7, 6,7, 7};
 
-__device__ __forceinline__ uint32_t involve_mask(int x)
+// involve mask of selection item x: the pair slots that contain x
+constexpr uint32_t involve_mask(int x)
 {
+    constexpr uint8_t sx[28] = {0,0,0,0,0,0,0, 1,1,1,1,1,1, 2,2,2,2,2, 3,3,3,3, 4,4,4, 5,5, 6};
+    constexpr uint8_t sy[28] = {1,2,3,4,5,6,7, 2,3,4,5,6,7, 3,4,5,6,7, 4,5,6,7, 5,6,7, 6,7, 7};
     uint32_t m = 0;
-    #pragma unroll
     for (int s = 0; s < 28; ++s)
-        if (cSlotX[s] == x || cSlotY[s] == x)
+        if (sx[s] == x || sy[s] == x)
             m |= 1u << s;
     return m;
 }
+__constant__ uint32_t cInvolve[8] = {involve_mask(0), involve_mask(1), involve_mask(2), involve_mask(3),
+                                     involve_mask(4), involve_mask(5), involve_mask(6), involve_mask(7)};
 
 // Matching::solveConflicts (src/matching.hpp:99-141) on bit masks: conf = set of conflicting pair slots,
 // result = set of eliminated selection items.  In every conflict (first, second) the reference's edgeS is the
@@ -521,9 +525,7 @@ __device__ int32_t greedy_matching(unsigned long long const * keys, int K, int l
 {
     int L = lookahead;
     if (L > K) L = K; else if (L == 0) L = 5;                  // :153-156
-    uint32_t inv[kMaxLookahead];
-    #pragma unroll
-    for (int x = 0; x < kMaxLookahead; ++x) inv[x] = involve_mask(x);
+    uint32_t const * const inv = cInvolve;
     int32_t score = 0;
     int pos = 0;
     while (pos < K)

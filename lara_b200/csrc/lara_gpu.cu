@@ -61,6 +61,13 @@ struct Worker
     std::string err;
 };
 
+// Density of a sample of a device's pairs (edges, interactions and band bytes per matrix cell), measured by running
+// the set-up stages on it; sizes the batches (batch_limit).
+struct Pilot
+{
+    double cells = 0, edges = 0, inters = 0, dpBytes = 0;
+};
+
 // All device-side resources of one GPU.
 struct Device
 {
@@ -76,6 +83,7 @@ struct Device
     cudaEvent_t evRun0 = nullptr, evRun1 = nullptr;     // span of one run_device on the stream
     // share of the prepared pair list and its device-resident outputs
     std::vector<OrientedPair> pairs;
+    Pilot pilot;                            // densities of a sample of `pairs`
     PairOutHdr * dOutHdr = nullptr;
     int32_t * dOutLines = nullptr;
     int64_t * dOutOff = nullptr;
@@ -93,13 +101,15 @@ struct lara_ctx
     DevParams dp{};
     std::string err;
     std::deque<Device> devs;                // deque: Device holds a mutex and is not movable
-    int nWorkers = 3;                       // concurrent batches per device (env LARA_B200_WORKERS)
-    size_t batchPairsDefault = 32768;       // pairs per batch (env LARA_B200_BATCH)
+    int nWorkers = 2;                       // concurrent batches per device (env LARA_B200_WORKERS)
+    size_t batchPairsDefault = 56832;       // pairs per batch (env LARA_B200_BATCH): 148 SMs x 12 warps x 32 one-thread pairs
     bool bandMode = true;                   // band DP kernels where the active edges allow it (env LARA_B200_BAND=0: off)
     int bandMargin = 1;                     // diagonals added on both sides of the active range (env LARA_B200_MARGIN)
     int bandMaxW = 1024;                    // widest band; beyond it the full-matrix kernel runs (env LARA_B200_BANDMAXW)
     int bandMinWarps = 592;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
     int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
+    bool compactSlots = false;              // repack the DP slot lists as pairs finish (env LARA_B200_COMPACT=1); measured:
+                                            // the DP is HBM-bound, idle lanes cost nothing, repacking costs locality
     int postSmemCand = 256;                 // matching candidates sorted in shared memory (env LARA_B200_SMEMCAND)
     // host copy of the inputs (for pair orientation and batch sizing)
     int32_t nSeq = 0;
@@ -201,20 +211,23 @@ void choose_band(lara_ctx const & ctx, PairDesc & d)
 }
 
 // Lanes per pair G and diagonals per block Q for the nPairs pairs of a batch that share the band width W:
-// Q = 16 (G = W / 32, down to one thread per pair) when that still fills the machine, else Q = 4 (G = W / 8).
+// Q = 16 (G = W / 32, down to one thread per pair) when that still fills the machine, else Q = 8 (G = W / 16),
+// else Q = 4 (G = W / 8).
 void choose_band_shape(lara_ctx const & ctx, int W, int nPairs, int & G, int & Q)
 {
-    int const g16 = W / 32, g4 = W / 8;
-    int64_t const warps16 = ((int64_t)nPairs * g16 + 31) / 32;
-    Q = (g4 > 32 || warps16 >= ctx.bandMinWarps) ? 16 : 4;
+    int const g16 = W / 32, g8 = W / 16, g4 = W / 8;
+    int64_t const warps16 = ((int64_t)nPairs * g16 + 31) / 32, warps8 = ((int64_t)nPairs * g8 + 31) / 32;
+    Q = (g8 > 32 || warps16 >= ctx.bandMinWarps) ? 16 : ((g4 > 32 || warps8 >= ctx.bandMinWarps) ? 8 : 4);
     if (ctx.bandForceQ == 16 || (ctx.bandForceQ == 8 && W <= 512) || (ctx.bandForceQ == 4 && g4 <= 32)) Q = ctx.bandForceQ;
     G = W / (2 * Q);
 }
 
 // ---------------------------------------------------------------------------------------------------
-// One batch: pairs [begin, end) of dv.pairs (already length sorted).
+// One batch: pairs [begin, end) of dv.pairs (already length sorted).  With `pilot` the pairs are pilotPairs[0..n):
+// only the set-up stages up to the counts run, and the densities are returned.
 // ---------------------------------------------------------------------------------------------------
-void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t end)
+void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t end, Pilot * pilot = nullptr,
+               OrientedPair const * pilotPairs = nullptr)
 {
     int const n = (int)(end - begin);
     DevParams const & dp = ctx.dp;
@@ -227,7 +240,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     {
         for (int i = 0; i < n; ++i)
         {
-            OrientedPair const & op = dv.pairs[begin + i];
+            OrientedPair const & op = pilot ? pilotPairs[i] : dv.pairs[begin + i];
             PairDesc & d = desc[(size_t)i];
             if (!commit)
             {
@@ -357,9 +370,12 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         d.offEdge = rB.take(4ll * d.E);
         if (d.bandW > 0)
         {
-            ++wk.stats.reserved[1];                     // pairs solved by the band kernels
-            if (d.bandQ == 16) ++wk.stats.reserved[2];  // ... of those in blocks of 16 diagonals
-            wk.stats.reserved[3] += d.bandW;            // sum of their band widths
+            if (!pilot)
+            {
+                ++wk.stats.reserved[1];                     // pairs solved by the band kernels
+                if (d.bandQ == 16) ++wk.stats.reserved[2];  // ... of those in blocks of 16 diagonals
+                wk.stats.reserved[3] += d.bandW;            // sum of their band widths
+            }
         }
         else
         {
@@ -386,6 +402,25 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     wk.stats.kernel_launches += 1;
+    if (pilot)
+    {
+        for (int i = 0; i < n; ++i)
+        {
+            PairDesc const & d = desc[(size_t)i];
+            pilot->cells += (double)d.la * d.lb;
+            pilot->edges += d.E;
+            pilot->inters += d.D;
+            // scores + trace + closed-form records of the band, or stream + trace of the full-matrix kernel
+            pilot->dpBytes += d.bandW > 0 ? 4.6 * d.bandW * (d.lb + 1) + 16.0 * (d.la + d.lb + 2)
+                                          : 4.0 * d.nVals + 128.0 * d.nSteps * d.W;
+        }
+        CK(cudaFreeAsync(rB.ptr, s));
+        CK(cudaFreeAsync(rA.ptr, s));
+        CK(cudaFreeAsync(dState, s));
+        CK(cudaFreeAsync(dDesc, s));
+        CK(cudaStreamSynchronize(s));
+        return;
+    }
     int64_t sizeC = 0;
     for (int i = 0; i < n; ++i) sizeC += 14 * align4(std::max(desc[(size_t)i].D, 1)) + 8 + align4(std::max(desc[(size_t)i].nVals, 1));
     Region rC;
@@ -432,9 +467,16 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         wk.aux.push_back(st); wk.auxJoin.push_back(ev);
     }
+    // two copies of the slot lists (the DP launches read one, a compaction writes the other) + one counter per class
     int32_t * dIdx = nullptr;
-    CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * std::max<size_t>(idxAll.size(), 1), s));
+    size_t const idxStride = std::max<size_t>(idxAll.size(), 1);
+    CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * (2 * idxStride + cls.size() + 1), s));
     CK(cudaMemcpyAsync(dIdx, idxAll.data(), sizeof(int32_t) * idxAll.size(), cudaMemcpyHostToDevice, s));
+    int32_t * const dCounts = dIdx + 2 * idxStride;
+    std::vector<int> clsSide(cls.size(), 0), clsCount(cls.size());
+    std::vector<int32_t> hCounts(cls.size());
+    for (size_t k = 0; k < cls.size(); ++k) clsCount[k] = std::get<2>(cls[k]);
+    int lastCompactActive = n;
     *wk.hActive = n;
     CK(cudaMemcpyAsync(wk.dActive, wk.hActive, sizeof(int32_t), cudaMemcpyHostToDevice, s));
 
@@ -463,12 +505,13 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
             auto const & c = cls[k];
             cudaStream_t const sk = k == 0 ? s : wk.aux[k - 1];
             if (k > 0) CK(cudaStreamWaitEvent(sk, wk.evFork, 0));
+            int32_t const * const lst = dIdx + (size_t)clsSide[k] * idxStride + std::get<1>(c);
+            if (clsCount[k] == 0) continue;
             if (std::get<3>(c) >= 0)
-                CK(launch_gotoh_band(bandClasses[(size_t)std::get<3>(c)].G, bandClasses[(size_t)std::get<3>(c)].Q, std::get<2>(c),
-                                     dIdx + std::get<1>(c), dDesc, dState, arena, dp.go, dp.ge, sk));
+                CK(launch_gotoh_band(bandClasses[(size_t)std::get<3>(c)].G, bandClasses[(size_t)std::get<3>(c)].Q, clsCount[k],
+                                     lst, dDesc, dState, arena, dp.go, dp.ge, sk));
             else
-                CK(launch_gotoh_fill(std::get<0>(c), std::get<2>(c), dIdx + std::get<1>(c), dDesc, dState, arena, dv.negBuf,
-                                     dp.go, dp.ge, sk));
+                CK(launch_gotoh_fill(std::get<0>(c), clsCount[k], lst, dDesc, dState, arena, dv.negBuf, dp.go, dp.ge, sk));
             if (k > 0) CK(cudaEventRecord(wk.auxJoin[k - 1], sk));
             wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
         }
@@ -484,6 +527,19 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
             CK(cudaMemcpyAsync(wk.hActive, wk.dActive, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
             CK(cudaStreamSynchronize(s));
             if (*wk.hActive <= 0) break;
+            // finished pairs leave holes in the warps of the DP kernels: repack the slot lists now and then
+            if (ctx.compactSlots && (int64_t)*wk.hActive * 10 < (int64_t)lastCompactActive * 9)
+            {
+                CK(cudaMemsetAsync(dCounts, 0, sizeof(int32_t) * cls.size(), s));
+                for (size_t k = 0; k < cls.size(); ++k)
+                    CK(launch_compact_slots(clsCount[k], dIdx + (size_t)clsSide[k] * idxStride + std::get<1>(cls[k]), dState,
+                                            dIdx + (size_t)(1 - clsSide[k]) * idxStride + std::get<1>(cls[k]), dCounts + k, s));
+                CK(cudaMemcpyAsync(hCounts.data(), dCounts, sizeof(int32_t) * cls.size(), cudaMemcpyDeviceToHost, s));
+                CK(cudaStreamSynchronize(s));
+                for (size_t k = 0; k < cls.size(); ++k) { clsSide[k] = 1 - clsSide[k]; clsCount[k] = hCounts[k]; }
+                wk.stats.kernel_launches += (int64_t)cls.size();
+                lastCompactActive = *wk.hActive;
+            }
             nextPoll = nextPoll < 16 ? nextPoll * 2 : nextPoll + 16;
         }
     }
@@ -523,17 +579,21 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers)
 {
     size_t freeB = 0, totalB = 0;
     cudaMemGetInfo(&freeB, &totalB);
-    double const budget = 0.6 * (double)totalB / (double)nWorkers;
+    double const budget = 0.55 * (double)totalB / (double)nWorkers;
     double used = 0;
     size_t k = begin;
     size_t const hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : ctx.batchPairsDefault;
+    // densities measured on a sample of this device's pairs (run_device), with a safety factor
+    double const ePerCell = 1.3 * dv.pilot.edges / std::max(dv.pilot.cells, 1.0);
+    double const dPerCell = 1.3 * dv.pilot.inters / std::max(dv.pilot.cells, 1.0);
+    double const dpPerCell = 1.3 * dv.pilot.dpBytes / std::max(dv.pilot.cells, 1.0);
     while (k < dv.pairs.size() && k - begin < hardCap)
     {
         OrientedPair const & op = dv.pairs[k];
         double const C = (double)op.la * op.lb;
-        // bytes: filter scratch 4 C (set-up only); bitmap, edges (E <= ~0.2 C, 5 arrays), interactions (D <= ~3 E,
-        // 6 arrays), band arrays or full-matrix trace, lines: generously 16 C + 3 KB per residue
-        double const per = 4.0 * C + 16.0 * C + 3072.0 * (op.la + op.lb);
+        // bytes: filter scratch 4 C (set-up only) + bitmap C / 8 + per edge 36 + per interaction 56 + DP arrays
+        // + lines, candidates, row starts
+        double const per = 4.0 * C + C / 8 + (36.0 * ePerCell + 56.0 * dPerCell + dpPerCell) * C + 64.0 * (op.la + op.lb) + 4096;
         if (used + per > budget && k > begin) break;
         used += per;
         ++k;
@@ -579,6 +639,16 @@ void run_device(lara_ctx & ctx, Device & dv)
         nW = std::max(1, std::min(nW, (int)dv.workers.size()));
         dv.nextBegin = 0;
         for (Worker & wk : dv.workers) { std::memset(&wk.stats, 0, sizeof(wk.stats)); wk.err.clear(); }
+        // pilot: set-up stages on a sample of the pairs -> densities for the batch sizes
+        if (dv.pilot.cells == 0 && !dv.pairs.empty())
+        {
+            size_t const nS = std::min<size_t>(dv.pairs.size(), 256);
+            std::vector<OrientedPair> sample(nS);
+            for (size_t i = 0; i < nS; ++i) sample[i] = dv.pairs[i * dv.pairs.size() / nS];
+            lara_stats const keep = dv.workers[0].stats;
+            run_batch(ctx, dv, dv.workers[0], 0, nS, &dv.pilot, sample.data());
+            dv.workers[0].stats = keep;
+        }
         CK(cudaEventRecord(dv.evRun0, dv.stream));
         // the other workers' streams start after the start event
         for (int w = 1; w < nW; ++w) CK(cudaStreamWaitEvent(dv.workers[(size_t)w].stream, dv.evRun0, 0));
@@ -679,6 +749,7 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_BANDMAXW")) ctx->bandMaxW = std::max(0, std::min(1024, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BANDMINWARPS")) ctx->bandMinWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BANDQ")) ctx->bandForceQ = std::atoi(e);
+    if (char const * e = std::getenv("LARA_B200_COMPACT")) ctx->compactSlots = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_SMEMCAND")) ctx->postSmemCand = std::max(32, std::min(2048, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
     ctx->P = *params;
@@ -866,7 +937,7 @@ int lara_gpu_prepare_pairs(lara_ctx * ctx, int64_t n_pairs, int32_t const * idx_
             Device & dv = ctx->devs[k];
             CK(cudaSetDevice(dv.id));
             device_free_outputs(dv);
-            dv.pairs.clear();
+            dv.pairs.clear(); dv.pilot = Pilot{};
             for (size_t q = k; q < all.size(); q += nd) dv.pairs.push_back(all[q]);   // interleaved shares
             dv.outOff.assign(dv.pairs.size() + 1, 0);
             for (size_t q = 0; q < dv.pairs.size(); ++q) dv.outOff[q + 1] = dv.outOff[q] + 3ll * dv.pairs[q].lb;

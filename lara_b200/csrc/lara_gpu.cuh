@@ -155,6 +155,9 @@ cudaError_t launch_gotoh_fill(int R, int n, int32_t const * pairIdx, PairDesc co
 cudaError_t launch_gotoh_band(int G, int Q, int nSlots, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t go, int32_t ge, cudaStream_t stream);
 bool band_shape_supported(int G, int Q);
+// out = the entries p >= 0 of in[0..n) whose pair has not finished, *count += their number (count zeroed by the caller)
+cudaError_t launch_compact_slots(int n, int32_t const * in, PairState const * state, int32_t * out, int32_t * count,
+                                 cudaStream_t stream);
 // position (in ints, relative to offBVals) of the score of band cell (row r, diagonal index x)
 __host__ __device__ inline int64_t band_val_index(int bandW, int ppw, int slot, int r, int x)
 {
