@@ -73,3 +73,36 @@ def test_solve_300nt(built):
     files = util.make_input(seed=36, n=5, length=300)
     got, want, _ = _solve_both(files, num_iterations=80, max_nondecreasing=10)
     assert util.results_equal(got, want) is None, util.results_equal(got, want)
+
+
+def test_solve_long_sequences(built):
+    """Shorter sequence beyond the single-pass full-matrix kernel (640 nt): band kernels only (BASELINE config C4)."""
+    files = util.make_input(seed=37, n=3, length=800, lenmax=900, fmt="dp")
+    got, want, st = _solve_both(files, num_iterations=30, max_nondecreasing=5)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+    assert st.reserved[1] == 3                      # all three pairs ran banded
+
+
+def test_solve_skewed_lengths(built):
+    """Lognormal lengths 50..600 (BASELINE config C5): mixed band widths and launch classes in one batch."""
+    files = util.make_input(seed=38, n=14, length=0, skew=True)
+    got, want, _ = _solve_both(files, num_iterations=40, max_nondecreasing=6)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+
+
+@pytest.mark.parametrize("env", [
+    dict(LARA_B200_BAND="0"),
+    dict(LARA_B200_BANDQ="4"),
+    dict(LARA_B200_BANDQ="8"),
+    dict(LARA_B200_BANDQ="16"),
+    dict(LARA_B200_BANDQ="16", LARA_B200_COMPACT="1", LARA_B200_BATCH="40", LARA_B200_WORKERS="3"),
+    dict(LARA_B200_BANDMAXW="32", LARA_B200_BATCH="33"),
+])
+def test_solve_kernel_variants(built, env, monkeypatch):
+    """Every DP kernel family and the scheduling switches give the same bits: full matrix, band blocks of 4 / 8 / 16
+    diagonals, compacted slot lists, several small batches on concurrent workers, band / full-matrix mixes."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    files = util.make_input(seed=39, n=12, length=90, lenmax=200)
+    got, want, _ = _solve_both(files, num_iterations=120, max_nondecreasing=10)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
