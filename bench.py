@@ -14,9 +14,11 @@ Prints ONE JSON line (rank 0).  Keys beyond the base contract:
   e2e          the same metric through the C ABI with HOST buffers (lara_gpu_set_sequences + lara_gpu_solve_pairs
                + results copied to host memory), wall clock, every step
   gcups        DP cell updates/s (sum over pairs and iterations of lenA*lenB) / 1e9
-  roofline     DP fill kernel: achieved = 9 int32 ops per cell * cells / summed CUDA-event
-               duration of the DP launches; peak = int32 lane-op issue rate measured on this GPU by the library's
-               microbenchmark; plus the kernel's algorithmic HBM traffic against MEASURED_PEAKS.json
+  roofline     DP fill kernel (banded Gotoh, HBM bound): achieved = algorithmic bytes of the DP launches (4.5 B per band
+               cell + 16 B closed-form record per row and column) / summed CUDA-event duration of the launches, against
+               MEASURED_PEAKS.json hbm_gbs; `isolated` = the same from one extra single-worker step (no overlap with the
+               other worker's kernels); int32_issue = 9 algorithmic ops per band cell against the issue
+               rate measured on this GPU by the library's microbenchmark
   cpu_baseline the UNMODIFIED reference binary (oracle/_ref/lara_scalar, built from /root/reference by
                oracle/build_ref.sh) on this box's host cores, on a bounded sample of the same workload
 """
@@ -188,7 +190,7 @@ def workload_config(args, w, world):
                            {"c1": 0, "c2": 1, "c3": 2}[args.workload]),
             "n_sequences": w["n"], "length": w["length"], "pairs": w["n"] * (w["n"] - 1) // 2,
             "num_iterations": 500, "partition": "round-robin over the length-sorted pair list, %d rank(s)" % world,
-            "l2": "per-batch working set (trace + multipliers) is larger than L2; no explicit flush"}
+            "l2": "per-batch working set (band scores, trace, interaction records: > 10 GB) is larger than L2; no explicit flush"}
 
 
 def main():
@@ -201,6 +203,7 @@ def main():
     ap.add_argument("--nseq", type=int, default=0, help="developer switch: only the first NSEQ sequences")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-isolated", action="store_true", help="skip the extra single-worker step of the roofline")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -274,6 +277,7 @@ def main():
     dev_ms = 0.0
     dp_ms = post_ms = setup_ms = 0.0
     cells = 0
+    dp_bytes = dp_cells_band = dp_pair_iters = 0
     launches = dp_launches = 0
     wall0 = time.perf_counter()
     for _ in range(args.steps):
@@ -286,6 +290,9 @@ def main():
         cells += st.dp_cells
         launches += st.kernel_launches
         dp_launches += st.dp_launches
+        dp_bytes += st.reserved[4]
+        dp_cells_band += st.reserved[5]
+        dp_pair_iters += st.sum_iterations
         log("step: %.1f ms device, dp %.1f post %.1f setup %.1f (summed over %d concurrent workers), band pairs %d (32-diag %d) of %d, "
             "mean iterations %.1f, E/pair %.0f, D/pair %.0f"
             % (st.ms_device, st.ms_dp, st.ms_bounds, st.ms_setup, st.reserved[0], st.reserved[1], st.reserved[2], st.n_pairs,
@@ -326,35 +333,68 @@ def main():
             dist.destroy_process_group()
         return 0
 
-    # ---- roofline of the dominant kernel (DP fill) ------------------------------------------------
+    # ---- roofline of the metric's kernel (DP fill) -------------------------------------------------
+    # bound: HBM.  achieved = algorithmic bytes of the DP launches (per band cell 4 B score + 0.5 B trace nibble, plus one
+    # 16 B closed-form record per row and column; lara_stats.reserved[4]) / summed CUDA-event durations of the DP
+    # launches.  With two workers the launches of one batch overlap the post kernel of the other, so the
+    # in-region figure is a lower bound; `isolated` repeats one step with a single worker (launches back to back).
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    int_rates = {k: ctx.int_issue_rate(k) for k in (0, 1, 2)}
-    int_peak = max(int_rates.values())
-    dp_cells_rank0 = float(cells)
-    achieved_gops = dp_cells_rank0 * OPS_PER_CELL / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else 0.0
-    st = ctx.stats()
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    int_rates = {k: ctx.int_issue_rate(k) for k in (0, 1, 2)}
+    iso = None
+    if not multi_proc and args.gpus == 1 and not args.no_isolated:
+        os.environ["LARA_B200_WORKERS"] = "1"
+        ctx1 = lb.Context(params, device_ids=device_ids)
+        os.environ.pop("LARA_B200_WORKERS", None)
+        ctx1.set_sequences(flat)
+        ctx1.prepare_pairs(my_a, my_b)
+        ctx1.run_prepared()
+        s1 = ctx1.stats()
+        iso = {"dp_ms": s1.ms_dp, "post_ms": s1.ms_bounds, "setup_ms": s1.ms_setup, "device_ms": s1.ms_device,
+               "dp_launches": s1.dp_launches, "dp_bytes": s1.reserved[4], "dp_cells_band": s1.reserved[5],
+               "dp_cells": s1.dp_cells}
+        ctx1.close()
+    achieved = dp_bytes / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else 0.0
     roofline = {
-        "kernel": "gotoh_fill_kernel", "bound": "int32_issue", "achieved": achieved_gops, "peak": int_peak,
-        "unit": "Gop/s", "frac": achieved_gops / int_peak if int_peak else None,
-        "peak_source": "measured on this GPU: lara_gpu_int_issue_rate (IADD %.0f, LOP3+VIMNMX %.0f, DP mix %.0f Gop/s)"
-                       % (int_rates[0], int_rates[1], int_rates[2]),
-        "ops_per_cell": OPS_PER_CELL, "dp_gcups_kernel_only": dp_cells_rank0 / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else None,
-        "dp_launches": dp_launches, "dp_ms_per_launch": dp_ms / dp_launches if dp_launches else None,
+        "kernel": "gotoh_band_kernel", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        "frac": achieved / hbm_peak if hbm_peak else None,
+        "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+        "algorithmic_bytes": "4.5 B per band cell (4 B score read + 4-bit trace write) + 16 B closed-form record per row and column",
+        "timing": "sum of CUDA-event spans of the %d DP launches of the timed region (%d concurrent workers: spans include "
+                  "time shared with the other worker's kernels)" % (dp_launches, int(st.reserved[0])),
+        "dp_ms_per_launch": dp_ms / dp_launches if dp_launches else None,
+        "dp_gcups_kernel_only": float(cells) / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else None,
+        "band_cells_per_matrix_cell": dp_cells_band / float(cells) if cells else None,
         "traffic": None,
-        "hbm": {"algorithmic_bytes_per_cell": 1.3, "achieved_gbs": dp_cells_rank0 * 1.3 / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else None,
-                "peak_gbs": hbm_peak, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+        "int32_issue": {"ops_per_band_cell": OPS_PER_CELL, "achieved_gops": dp_cells_band * OPS_PER_CELL / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else None,
+                        "peak_gops": max(int_rates.values()),
+                        "peak_source": "lara_gpu_int_issue_rate on this GPU (IADD %.0f, LOP3+VIMNMX %.0f, DP mix %.0f Gop/s)"
+                                       % (int_rates[0], int_rates[1], int_rates[2])},
         "share_of_step": {"dp": dp_ms / dev_ms if dev_ms else None, "post": post_ms / dev_ms if dev_ms else None,
                           "setup": setup_ms / dev_ms if dev_ms else None},
     }
+    if iso:
+        a1 = iso["dp_bytes"] / (iso["dp_ms"] * 1e-3) / 1e9
+        roofline["isolated"] = {
+            "achieved": a1, "frac": a1 / hbm_peak, "dp_ms_per_launch": iso["dp_ms"] / max(iso["dp_launches"], 1),
+            "dp_gcups_kernel_only": iso["dp_cells"] / (iso["dp_ms"] * 1e-3) / 1e9,
+            "pairs_per_s": n_pairs_total / (iso["device_ms"] * 1e-3),
+            "share_of_step": {"dp": iso["dp_ms"] / iso["device_ms"], "post": iso["post_ms"] / iso["device_ms"],
+                              "setup": iso["setup_ms"] / iso["device_ms"]},
+            "timing": "one extra step with a single worker: launches back to back on one stream"}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:
-            roofline["traffic"] = json.load(open(prof)).get("gotoh_fill_kernel_dram_bytes_per_launch")
+            t = json.load(open(prof))
+            # ncu: dram__bytes_read.sum + dram__bytes_write.sum of one DP launch, scaled to this run's average launch
+            per_pair = t["gotoh_band_kernel"]["dram_bytes"] / t["gotoh_band_kernel"]["pairs_in_launch"]
+            roofline["traffic"] = per_pair * (dp_pair_iters / dp_launches) if dp_launches else None
+            roofline["traffic_source"] = t["gotoh_band_kernel"].get("source")
+            roofline["algorithmic_bytes_per_launch"] = dp_bytes / dp_launches if dp_launches else None
         except Exception:
             pass
 

@@ -1005,6 +1005,34 @@ cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state,
     return cudaGetLastError();
 }
 
+// Result gather: the lines of pair q (slot of 3 * lb ints: posLow | posHigh | weight) -> three dense arrays at dstOff[q]
+__global__ void pack_lines_kernel(int n, PairOutHdr const * __restrict__ hdr, int32_t const * __restrict__ outLines,
+                                  int64_t const * __restrict__ outOff, int64_t const * __restrict__ dstOff,
+                                  int32_t * __restrict__ low, int32_t * __restrict__ high, int32_t * __restrict__ weight)
+{
+    int const q = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
+    int const lane = threadIdx.x & 31;
+    if (q >= n) return;
+    int64_t const o = outOff[q];
+    int const lb = (int)((outOff[q + 1] - o) / 3), nl = hdr[q].nLines;
+    int32_t const * __restrict__ src = outLines + o;
+    int64_t const d = dstOff[q];
+    for (int i = lane; i < nl; i += 32)
+    {
+        low[d + i] = src[i];
+        high[d + i] = src[lb + i];
+        weight[d + i] = src[2 * lb + i];
+    }
+}
+
+cudaError_t launch_pack_lines(int n, PairOutHdr const * hdr, int32_t const * outLines, int64_t const * outOff,
+                              int64_t const * dstOff, int32_t * low, int32_t * high, int32_t * weight, cudaStream_t stream)
+{
+    if (n <= 0) return cudaSuccess;
+    pack_lines_kernel<<<(n + 7) / 8, 256, 0, stream>>>(n, hdr, outLines, outOff, dstOff, low, high, weight);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                   int32_t go, int32_t ge, int maxLa, int maxLb, cudaStream_t stream)
 {

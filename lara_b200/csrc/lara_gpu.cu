@@ -15,6 +15,7 @@
 #include <cstring>
 #include <deque>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <stdexcept>
 #include <tuple>
@@ -127,8 +128,10 @@ namespace
 struct ResultOwner
 {
     std::vector<lara_pair_result> pairs;
-    std::vector<int32_t> posLow, posHigh;
-    std::vector<uint32_t> weight;
+    // not value-initialised: the device-to-host copies write every element
+    std::unique_ptr<int32_t[]> posLow, posHigh;
+    std::unique_ptr<uint32_t[]> weight;
+    int64_t nLines = 0;
 };
 
 DevParams make_dev_params(lara_params const & P)
@@ -557,6 +560,14 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         int64_t const its = ctx.P.num_iterations - hState[(size_t)i].remaining;
         wk.stats.sum_iterations += its;
         wk.stats.dp_cells += its * (int64_t)desc[(size_t)i].la * desc[(size_t)i].lb;
+        {
+            // algorithmic HBM bytes of the DP launches: band: 4 B score + 0.5 B trace per band cell and
+            // 16 B closed-form record per row and column; full matrix: 1.3 B per cell (sparse stream + trace)
+            PairDesc const & d = desc[(size_t)i];
+            wk.stats.reserved[4] += d.bandW > 0 ? its * (int64_t)(4.5 * d.bandW * d.lb + 16.0 * (d.la + d.lb + 2))
+                                                : its * (int64_t)(1.3 * d.la * d.lb);
+            wk.stats.reserved[5] += d.bandW > 0 ? its * (int64_t)d.bandW * d.lb : its * (int64_t)d.la * d.lb;   // cells computed
+        }
     }
     wk.stats.ms_setup += ev_ms(evS0, evS1);
     for (int it = 0; it < itersRun; ++it)
@@ -682,6 +693,8 @@ void run_device(lara_ctx & ctx, Device & dv)
             dv.stats.reserved[1] += dv.workers[(size_t)w].stats.reserved[1];
             dv.stats.reserved[2] += dv.workers[(size_t)w].stats.reserved[2];
             dv.stats.reserved[3] += dv.workers[(size_t)w].stats.reserved[3];
+            dv.stats.reserved[4] += dv.workers[(size_t)w].stats.reserved[4];
+            dv.stats.reserved[5] += dv.workers[(size_t)w].stats.reserved[5];
         }
     }
     catch (std::exception const & e)
@@ -990,6 +1003,8 @@ int lara_gpu_run_prepared(lara_ctx * ctx)
         agg.reserved[1] += dv.stats.reserved[1];                               // pairs solved by the band kernels
         agg.reserved[2] += dv.stats.reserved[2];                               // ... in blocks of 16 diagonals
         agg.reserved[3] += dv.stats.reserved[3];                               // sum of the band widths
+        agg.reserved[4] += dv.stats.reserved[4];                               // algorithmic HBM bytes of the DP launches
+        agg.reserved[5] += dv.stats.reserved[5];                               // DP cells actually computed
     }
     agg.ms_total = ms;
     ctx->stats = agg;
@@ -1005,53 +1020,81 @@ int lara_gpu_fetch_prepared(lara_ctx * ctx, lara_results * out)
     own->pairs.resize((size_t)ctx->nPrepared);
     try
     {
-        struct Got { std::vector<PairOutHdr> hdr; std::vector<int32_t> lines; };
-        std::vector<Got> got(ctx->devs.size());
+        // 1. headers of all devices -> number of lines per pair, position of each pair's lines in the result arrays
+        //    (device by device, in the device's own pair order; lara_pair_result::lines_off says where)
+        std::vector<std::vector<PairOutHdr>> hdr(ctx->devs.size());
+        std::vector<std::vector<int64_t>> dstOff(ctx->devs.size());
+        std::vector<int64_t> devBase(ctx->devs.size() + 1, 0);
         int64_t d2h = 0;
-        double msD2h = 0;
         for (size_t k = 0; k < ctx->devs.size(); ++k)
         {
             Device & dv = ctx->devs[k];
             CK(cudaSetDevice(dv.id));
-            got[k].hdr.resize(dv.pairs.size());
-            got[k].lines.resize((size_t)dv.outLinesTotal);
-            CK(cudaEventRecord(dv.events[0], dv.stream));
+            hdr[k].resize(dv.pairs.size());
             if (!dv.pairs.empty())
-            {
-                CK(cudaMemcpyAsync(got[k].hdr.data(), dv.dOutHdr, sizeof(PairOutHdr) * dv.pairs.size(), cudaMemcpyDeviceToHost, dv.stream));
-                CK(cudaMemcpyAsync(got[k].lines.data(), dv.dOutLines, sizeof(int32_t) * (size_t)dv.outLinesTotal, cudaMemcpyDeviceToHost, dv.stream));
-            }
+                CK(cudaMemcpyAsync(hdr[k].data(), dv.dOutHdr, sizeof(PairOutHdr) * dv.pairs.size(), cudaMemcpyDeviceToHost, dv.stream));
+            CK(cudaStreamSynchronize(dv.stream));
+            dstOff[k].resize(dv.pairs.size() + 1);
+            int64_t run = 0;
+            for (size_t q = 0; q < dv.pairs.size(); ++q) { dstOff[k][q] = run; run += hdr[k][q].nLines; }
+            dstOff[k][dv.pairs.size()] = run;
+            devBase[k + 1] = devBase[k] + run;
+            d2h += (int64_t)(sizeof(PairOutHdr) * dv.pairs.size());
+        }
+        int64_t const total = devBase.back();
+        own->nLines = total;
+        own->posLow.reset(new int32_t[(size_t)std::max<int64_t>(total, 1)]);
+        own->posHigh.reset(new int32_t[(size_t)std::max<int64_t>(total, 1)]);
+        own->weight.reset(new uint32_t[(size_t)std::max<int64_t>(total, 1)]);
+        // 2. gather on the device, three dense copies per device
+        double msD2h = 0;
+        std::vector<int32_t *> scratch(ctx->devs.size(), nullptr);
+        for (size_t k = 0; k < ctx->devs.size(); ++k)
+        {
+            Device & dv = ctx->devs[k];
+            int64_t const nL = dstOff[k].back();
+            if (dv.pairs.empty() || nL == 0) continue;
+            CK(cudaSetDevice(dv.id));
+            int64_t * dDst = nullptr;
+            CK(cudaMallocAsync((void **)&scratch[k], sizeof(int32_t) * 3 * (size_t)nL, dv.stream));
+            CK(cudaMallocAsync((void **)&dDst, sizeof(int64_t) * dstOff[k].size(), dv.stream));
+            CK(cudaMemcpyAsync(dDst, dstOff[k].data(), sizeof(int64_t) * dstOff[k].size(), cudaMemcpyHostToDevice, dv.stream));
+            CK(cudaEventRecord(dv.events[0], dv.stream));
+            CK(launch_pack_lines((int)dv.pairs.size(), dv.dOutHdr, dv.dOutLines, dv.dOutOff, dDst, scratch[k], scratch[k] + nL,
+                                 scratch[k] + 2 * nL, dv.stream));
+            CK(cudaMemcpyAsync(own->posLow.get() + devBase[k], scratch[k], sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
+            CK(cudaMemcpyAsync(own->posHigh.get() + devBase[k], scratch[k] + nL, sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
+            CK(cudaMemcpyAsync(own->weight.get() + devBase[k], scratch[k] + 2 * nL, sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
             CK(cudaEventRecord(dv.events[1], dv.stream));
+            CK(cudaFreeAsync(dDst, dv.stream));
+            CK(cudaFreeAsync(scratch[k], dv.stream));
+            d2h += 12 * nL;
+        }
+        // 3. pair records in request order (while the copies run)
+        for (size_t k = 0; k < ctx->devs.size(); ++k)
+        {
+            Device & dv = ctx->devs[k];
+            for (size_t q = 0; q < dv.pairs.size(); ++q)
+            {
+                OrientedPair const & op = dv.pairs[q];
+                PairOutHdr const & h = hdr[k][q];
+                lara_pair_result & r = own->pairs[(size_t)op.request];
+                r.idx_low = std::min(op.first, op.second);
+                r.idx_high = std::max(op.first, op.second);
+                r.best_lower = h.bestLower; r.best_upper = h.bestUpper; r.iterations = h.iterations; r.n_lines = h.nLines;
+                r.lines_off = devBase[k] + dstOff[k][q];
+            }
+        }
+        for (size_t k = 0; k < ctx->devs.size(); ++k)
+        {
+            Device & dv = ctx->devs[k];
+            if (dv.pairs.empty() || dstOff[k].back() == 0) continue;
+            CK(cudaSetDevice(dv.id));
             CK(cudaStreamSynchronize(dv.stream));
             msD2h = std::max(msD2h, ev_ms(dv.events[0], dv.events[1]));
-            d2h += (int64_t)(sizeof(PairOutHdr) * dv.pairs.size() + sizeof(int32_t) * (size_t)dv.outLinesTotal);
         }
         ctx->stats.ms_d2h = msD2h;
         ctx->stats.d2h_bytes = d2h;
-        // request order
-        std::vector<std::pair<size_t, size_t>> where((size_t)ctx->nPrepared);
-        for (size_t k = 0; k < ctx->devs.size(); ++k)
-            for (size_t q = 0; q < ctx->devs[k].pairs.size(); ++q)
-                where[(size_t)ctx->devs[k].pairs[q].request] = {k, q};
-        for (int64_t p = 0; p < ctx->nPrepared; ++p)
-        {
-            size_t const k = where[(size_t)p].first, q = where[(size_t)p].second;
-            Device & dv = ctx->devs[k];
-            OrientedPair const & op = dv.pairs[q];
-            PairOutHdr const & h = got[k].hdr[q];
-            lara_pair_result & r = own->pairs[(size_t)p];
-            r.idx_low = std::min(op.first, op.second);
-            r.idx_high = std::max(op.first, op.second);
-            r.best_lower = h.bestLower; r.best_upper = h.bestUpper; r.iterations = h.iterations; r.n_lines = h.nLines;
-            r.lines_off = (int64_t)own->posLow.size();
-            int32_t const * base = got[k].lines.data() + dv.outOff[q];
-            for (int32_t x = 0; x < h.nLines; ++x)
-            {
-                own->posLow.push_back(base[x]);
-                own->posHigh.push_back(base[op.lb + x]);
-                own->weight.push_back((uint32_t)base[2 * op.lb + x]);
-            }
-        }
     }
     catch (std::exception const & ex)
     {
@@ -1060,10 +1103,10 @@ int lara_gpu_fetch_prepared(lara_ctx * ctx, lara_results * out)
     }
     out->n_pairs = ctx->nPrepared;
     out->pairs = own->pairs.data();
-    out->n_lines_total = (int64_t)own->posLow.size();
-    out->line_pos_low = own->posLow.data();
-    out->line_pos_high = own->posHigh.data();
-    out->line_weight = own->weight.data();
+    out->n_lines_total = own->nLines;
+    out->line_pos_low = own->posLow.get();
+    out->line_pos_high = own->posHigh.get();
+    out->line_weight = own->weight.get();
     out->owner_ = own;
     return LARA_OK;
 }

@@ -170,6 +170,9 @@ cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state,
 // traceback only (unit entry point lara_gpu_gotoh_batch)
 cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                   int32_t go, int32_t ge, int maxLa, int maxLb, cudaStream_t stream);
+// result gather: the used part of every pair's output slot -> dense posLow / posHigh / weight arrays at dstOff[q]
+cudaError_t launch_pack_lines(int n, PairOutHdr const * hdr, int32_t const * outLines, int64_t const * outOff,
+                              int64_t const * dstOff, int32_t * low, int32_t * high, int32_t * weight, cudaStream_t stream);
 // per-device one-time configuration of the post kernels (shared memory opt-in)
 cudaError_t post_configure_device();
 // set-up stage 1: edge filter -> bitmap, optimum score, E
