@@ -58,6 +58,9 @@ struct Worker
     std::vector<cudaStream_t> aux;
     std::vector<cudaEvent_t> auxJoin;
     cudaEvent_t evFork = nullptr;
+    // slab of the batch arrays: grown between batches only, so that the iteration loop never waits for the allocator
+    int32_t * slab = nullptr;
+    int64_t slabInts = 0;
     lara_stats stats{};
     std::string err;
 };
@@ -109,6 +112,7 @@ struct lara_ctx
     int bandMaxW = 1024;                    // widest band; beyond it the full-matrix kernel runs (env LARA_B200_BANDMAXW)
     int bandMinWarps = 592;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
     int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
+    int verbose = 0;                        // env LARA_B200_VERBOSE=1: host-side stage times of every batch on stderr
     bool compactSlots = false;              // repack the DP slot lists as pairs finish (env LARA_B200_COMPACT=1); measured:
                                             // the DP is HBM-bound, idle lanes cost nothing, repacking costs locality
     int postSmemCand = 256;                 // matching candidates sorted in shared memory (env LARA_B200_SMEMCAND)
@@ -230,9 +234,43 @@ void choose_band_shape(lara_ctx const & ctx, int W, int nPairs, int & G, int & Q
 // only the set-up stages up to the counts run, and the densities are returned.
 // ---------------------------------------------------------------------------------------------------
 void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t end, Pilot * pilot = nullptr,
-               OrientedPair const * pilotPairs = nullptr)
+               OrientedPair const * pilotPairs = nullptr, double slabHintBytes = 0)
 {
     int const n = (int)(end - begin);
+    // the four big regions of a batch live in the worker's slab: A (length dependent) | S (filter scratch), then B
+    // (per edge, band) and C (per interaction) over S once the filter has run.  A region that does not fit (the
+    // estimate was too low) falls back to the stream-ordered allocator.
+    if (slabHintBytes > 0 && (double)wk.slabInts * 4 < slabHintBytes)
+    {
+        CK(cudaStreamSynchronize(wk.stream));
+        CK(cudaFree(wk.slab));
+        wk.slab = nullptr; wk.slabInts = 0;
+        int64_t const want = ((int64_t)(slabHintBytes * 1.1 / 4) + 1023) & ~(int64_t)1023;
+        CK(cudaMalloc((void **)&wk.slab, (size_t)want * 4));
+        wk.slabInts = want;
+    }
+    std::vector<void *> fallback;
+    auto region_alloc = [&](Region & rg, int64_t sizeInts, int64_t atInts)
+    {
+        if (slabHintBytes > 0 && wk.slab && atInts + sizeInts <= wk.slabInts)
+            rg.ptr = wk.slab + atInts;
+        else
+        {
+            CK(cudaMallocAsync((void **)&rg.ptr, (size_t)std::max<int64_t>(sizeInts, 1) * 4, wk.stream));
+            fallback.push_back(rg.ptr);
+        }
+        rg.size = sizeInts;
+    };
+    auto al256 = [](int64_t x) { return (x + 63) & ~(int64_t)63; };
+    auto tPrev = std::chrono::steady_clock::now();
+    auto lap = [&](char const * what)
+    {
+        if (!ctx.verbose) return;
+        auto const now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[lara_b200] dev %d batch %zu+%d %-28s %8.2f ms\n", dv.id, begin, n, what,
+                     std::chrono::duration<double, std::milli>(now - tPrev).count());
+        tPrev = now;
+    };
     DevParams const & dp = ctx.dp;
     cudaStream_t const s = wk.stream;
     std::vector<PairDesc> desc((size_t)n);
@@ -272,9 +310,9 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         layoutA(false, probe);
         sizeA = probe.used;
     }
+    lap("layout A (host)");
     Region rA;
-    CK(cudaMallocAsync((void **)&rA.ptr, (size_t)sizeA * 4, s));
-    rA.size = sizeA;
+    region_alloc(rA, sizeA, 0);
     int32_t * const arena = rA.ptr;
     layoutA(true, rA);
 
@@ -283,8 +321,8 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     {
         int64_t sizeS = 0;
         for (int i = 0; i < n; ++i) sizeS += align4((int64_t)desc[(size_t)i].la * desc[(size_t)i].lb + 6ll * (desc[(size_t)i].la + 1));
-        CK(cudaMallocAsync((void **)&rS.ptr, (size_t)sizeS * 4, s));
-        rS.size = sizeS; rS.baseDelta = rS.ptr - arena;
+        region_alloc(rS, sizeS, al256(sizeA));
+        rS.baseDelta = rS.ptr - arena;
         for (int i = 0; i < n; ++i)
             desc[(size_t)i].offScratch = rS.take((int64_t)desc[(size_t)i].la * desc[(size_t)i].lb + 6ll * (desc[(size_t)i].la + 1));
     }
@@ -296,13 +334,14 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     CK(cudaMemsetAsync(dState, 0, sizeof(PairState) * (size_t)n, s));
     CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
 
+    lap("alloc A + scratch");
     cudaEvent_t evS0 = wk.events[0], evS1 = wk.events[1];
     CK(cudaEventRecord(evS0, s));
     // ---- stage 1: edge filter -> E ------------------------------------------------------------------
     CK(launch_edge_filter(n, dDesc, dState, arena, dv.in, dp, s));
     CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
-    CK(cudaFreeAsync(rS.ptr, s));
     CK(cudaStreamSynchronize(s));
+    lap("edge filter (sync)");
     wk.stats.kernel_launches += 1;
     // ---- stage B layout: per-edge arrays, band geometry and warp groups of the band kernels --------------------
     std::map<int, std::vector<int32_t>> byW;               // band width -> pairs
@@ -362,9 +401,11 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     for (BandGroup const & g : groups)
         sizeB += align4((int64_t)g.rows * g.W * g.ppw) + align4((int64_t)g.rows * (g.W / 8) * g.ppw) +
                  4ll * g.ppw * (g.rows + g.cols);
+    lap("layout B (host)");
     Region rB;
-    CK(cudaMallocAsync((void **)&rB.ptr, (size_t)sizeB * 4, s));
-    rB.size = sizeB; rB.baseDelta = rB.ptr - arena;
+    region_alloc(rB, sizeB, al256(sizeA));
+    lap("alloc B");
+    rB.baseDelta = rB.ptr - arena;
     for (int i = 0; i < n; ++i)
     {
         PairDesc & d = desc[(size_t)i];
@@ -404,6 +445,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     CK(launch_setup_count(n, dDesc, dState, arena, dv.in, dp, s));
     CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
+    lap("set-up count (sync)");
     wk.stats.kernel_launches += 1;
     if (pilot)
     {
@@ -417,8 +459,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
             pilot->dpBytes += d.bandW > 0 ? 4.6 * d.bandW * (d.lb + 1) + 16.0 * (d.la + d.lb + 2)
                                           : 4.0 * d.nVals + 128.0 * d.nSteps * d.W;
         }
-        CK(cudaFreeAsync(rB.ptr, s));
-        CK(cudaFreeAsync(rA.ptr, s));
+        for (void * f : fallback) CK(cudaFreeAsync(f, s));
         CK(cudaFreeAsync(dState, s));
         CK(cudaFreeAsync(dDesc, s));
         CK(cudaStreamSynchronize(s));
@@ -427,8 +468,9 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     int64_t sizeC = 0;
     for (int i = 0; i < n; ++i) sizeC += 14 * align4(std::max(desc[(size_t)i].D, 1)) + 8 + align4(std::max(desc[(size_t)i].nVals, 1));
     Region rC;
-    CK(cudaMallocAsync((void **)&rC.ptr, (size_t)sizeC * 4, s));
-    rC.size = sizeC; rC.baseDelta = rC.ptr - arena;
+    region_alloc(rC, sizeC, al256(sizeA) + al256(sizeB));
+    lap("alloc C");
+    rC.baseDelta = rC.ptr - arena;
     for (int i = 0; i < n; ++i)
     {
         PairDesc & d = desc[(size_t)i];
@@ -546,6 +588,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
             nextPoll = nextPoll < 16 ? nextPoll * 2 : nextPoll + 16;
         }
     }
+    lap("iterations (enqueue + polls)");
     // error flags
     std::vector<PairState> hState((size_t)n);
     CK(cudaMemcpyAsync(hState.data(), dState, sizeof(PairState) * (size_t)n, cudaMemcpyDeviceToHost, s));
@@ -577,23 +620,29 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     }
     wk.stats.n_pairs += n;
     CK(cudaFreeAsync(dIdx, s));
-    CK(cudaFreeAsync(rC.ptr, s));
-    CK(cudaFreeAsync(rB.ptr, s));
-    CK(cudaFreeAsync(rA.ptr, s));
+    for (void * f : fallback) CK(cudaFreeAsync(f, s));
     CK(cudaFreeAsync(dState, s));
     CK(cudaFreeAsync(dDesc, s));
 }
 
 // Pairs per batch from the free device memory and a per-pair estimate (exact for the length dependent
 // part, heuristic for the edge/interaction arrays whose sizes are only known after set-up).
-size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers)
+size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers, double & bytes)
 {
     size_t freeB = 0, totalB = 0;
     cudaMemGetInfo(&freeB, &totalB);
     double const budget = 0.55 * (double)totalB / (double)nWorkers;
     double used = 0;
     size_t k = begin;
-    size_t const hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : ctx.batchPairsDefault;
+    size_t hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : ctx.batchPairsDefault;
+    if (!ctx.batchPairsCap)
+    {
+        // equal batches, a multiple of the worker count of them, so that no worker ends with a small batch alone
+        size_t const N = dv.pairs.size();
+        size_t nB = (N + hardCap - 1) / hardCap;
+        nB = (nB + (size_t)nWorkers - 1) / (size_t)nWorkers * (size_t)nWorkers;
+        hardCap = std::max<size_t>((N + nB - 1) / nB, std::min<size_t>(N, 1024));
+    }
     // densities measured on a sample of this device's pairs (run_device), with a safety factor
     double const ePerCell = 1.3 * dv.pilot.edges / std::max(dv.pilot.cells, 1.0);
     double const dPerCell = 1.3 * dv.pilot.inters / std::max(dv.pilot.cells, 1.0);
@@ -609,6 +658,7 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers)
         used += per;
         ++k;
     }
+    bytes = used;
     return k;
 }
 
@@ -620,14 +670,15 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
         for (;;)
         {
             size_t begin, end;
+            double bytes = 0;
             {
                 std::lock_guard<std::mutex> lock(dv.queueMutex);
                 begin = dv.nextBegin;
                 if (begin >= dv.pairs.size()) break;
-                end = batch_limit(ctx, dv, begin, nWorkers);
+                end = batch_limit(ctx, dv, begin, nWorkers, bytes);
                 dv.nextBegin = end;
             }
-            run_batch(ctx, dv, wk, begin, end);
+            run_batch(ctx, dv, wk, begin, end, nullptr, nullptr, bytes);
         }
         CK(cudaEventRecord(wk.evDone, wk.stream));
         CK(cudaStreamSynchronize(wk.stream));
@@ -762,6 +813,7 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_BANDMAXW")) ctx->bandMaxW = std::max(0, std::min(1024, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BANDMINWARPS")) ctx->bandMinWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BANDQ")) ctx->bandForceQ = std::atoi(e);
+    if (char const * e = std::getenv("LARA_B200_VERBOSE")) ctx->verbose = std::atoi(e);
     if (char const * e = std::getenv("LARA_B200_COMPACT")) ctx->compactSlots = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_SMEMCAND")) ctx->postSmemCand = std::max(32, std::min(2048, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
@@ -845,6 +897,7 @@ void lara_gpu_destroy(lara_ctx * ctx)
             for (cudaEvent_t ev : wk.events) cudaEventDestroy(ev);
             if (wk.evDone) cudaEventDestroy(wk.evDone);
             if (wk.evFork) cudaEventDestroy(wk.evFork);
+            cudaFree(wk.slab);
             for (cudaEvent_t ev : wk.auxJoin) cudaEventDestroy(ev);
             for (cudaStream_t st : wk.aux) cudaStreamDestroy(st);
             if (wk.stream) cudaStreamDestroy(wk.stream);
