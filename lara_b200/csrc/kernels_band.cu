@@ -48,7 +48,6 @@ namespace
 {
 
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kPrefetchRows = 3;
 
 template <int Q> struct TraceUnit;
 template <> struct TraceUnit<4>  { using type = uint16_t; };
@@ -111,6 +110,7 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
     constexpr int NU = 2 * G;                                   // trace units per row
     constexpr int CQ = Q / 4;                                   // value chunks per block
     constexpr int TW = (Q + 7) / 8;
+    constexpr int kPrefetchRows = 48 / Q;                       // L2 prefetch distance: about the same time for every Q
     int const warp = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
     int const lane = threadIdx.x & 31;
     if (warp * PPW >= nSlots)

@@ -110,7 +110,7 @@ struct lara_ctx
     bool bandMode = true;                   // band DP kernels where the active edges allow it (env LARA_B200_BAND=0: off)
     int bandMargin = 1;                     // diagonals added on both sides of the active range (env LARA_B200_MARGIN)
     int bandMaxW = 1024;                    // widest band; beyond it the full-matrix kernel runs (env LARA_B200_BANDMAXW)
-    int bandMinWarps = 592;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
+    int bandMinWarps = 400;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
     int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
     int verbose = 0;                        // env LARA_B200_VERBOSE=1: host-side stage times of every batch on stderr
     bool compactSlots = false;              // repack the DP slot lists as pairs finish (env LARA_B200_COMPACT=1); measured:
