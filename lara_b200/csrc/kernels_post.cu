@@ -14,6 +14,8 @@
 // iteration order among tied tops is ascending partner id (rows are stored in that order).
 #include "lara_gpu.cuh"
 
+#include <cstdlib>
+
 namespace lara
 {
 
@@ -997,7 +999,10 @@ cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state,
                                 int32_t * activeCount, int maxLa, int maxLb, int smemCand, cudaStream_t stream)
 {
     if (n <= 0) return cudaSuccess;
-    int const warpsPerBlock = 4;
+    // one warp (= one pair) per block: pairs differ a lot in run time (finished pairs return at once, alignments
+    // differ in length), and single-warp blocks let the SM refill per pair (measured: 4 % faster step than 4 warps)
+    static int const warpsPerBlock = []() { char const * e = std::getenv("LARA_B200_POSTWARPS"); int v = e ? std::atoi(e) : 1;
+                                            return v == 2 || v == 4 ? v : 1; }();
     size_t const smem = post_smem_per_warp(maxLa, maxLb, smemCand) * warpsPerBlock;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
     iterate_post_kernel<false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, outHdr, outLines,
