@@ -43,6 +43,7 @@ WORKLOADS = {
     "c1": dict(seed=1, n=10, length=120, fmt="dbn"),
     "c2": dict(seed=2, n=100, length=150, fmt="ebpseq"),
     "c3": dict(seed=3, n=500, length=300, fmt="ebpseq"),
+    "c5": dict(seed=5, n=2000, length=0, fmt="ebpseq"),     # lengths 50..600, lognormal (developer runs: use --nseq)
 }
 
 
@@ -187,7 +188,7 @@ def reference_arm(args, rank, world):
 def workload_config(args, w, world):
     return {"workload": "%s: %d synthetic RNAs x %d nt %s, all %d pairs, 500 iterations (BASELINE.json configs[%d])"
                         % (args.workload, w["n"], w["length"], w["fmt"], w["n"] * (w["n"] - 1) // 2,
-                           {"c1": 0, "c2": 1, "c3": 2}[args.workload]),
+                           {"c1": 0, "c2": 1, "c3": 2, "c5": 4}[args.workload]),
             "n_sequences": w["n"], "length": w["length"], "pairs": w["n"] * (w["n"] - 1) // 2,
             "num_iterations": 500, "partition": "round-robin over the length-sorted pair list, %d rank(s)" % world,
             "l2": "per-batch working set (band scores, trace, interaction records: > 10 GB) is larger than L2; no explicit flush"}
@@ -293,9 +294,9 @@ def main():
         dp_bytes += st.reserved[4]
         dp_cells_band += st.reserved[5]
         dp_pair_iters += st.sum_iterations
-        log("step: %.1f ms device, dp %.1f post %.1f setup %.1f (summed over %d concurrent workers), band pairs %d (32-diag %d) of %d, "
+        log("step: %.1f ms device, dp %.1f post %.1f setup %.1f (summed over %d concurrent workers), band pairs %d (Q16 %d, mean width %.0f) of %d, "
             "mean iterations %.1f, E/pair %.0f, D/pair %.0f"
-            % (st.ms_device, st.ms_dp, st.ms_bounds, st.ms_setup, st.reserved[0], st.reserved[1], st.reserved[2], st.n_pairs,
+            % (st.ms_device, st.ms_dp, st.ms_bounds, st.ms_setup, st.reserved[0], st.reserved[1], st.reserved[2], st.reserved[3] / max(st.reserved[1], 1), st.n_pairs,
                st.sum_iterations / max(st.n_pairs, 1), st.n_active_edges / max(st.n_pairs, 1), st.n_interactions / max(st.n_pairs, 1)))
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - wall0)
