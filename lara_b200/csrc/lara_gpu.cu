@@ -504,6 +504,16 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         idxAll.insert(idxAll.end(), bandClasses[k].slots.begin(), bandClasses[k].slots.end());
     }
     std::stable_sort(cls.begin(), cls.end(), [](auto const & x, auto const & y) { return std::get<2>(x) > std::get<2>(y); });
+    if (ctx.verbose)
+        for (auto const & c : cls)
+        {
+            if (std::get<3>(c) >= 0)
+                std::fprintf(stderr, "[lara_b200]   DP class band G=%d Q=%d (W=%d): %d slots\n", bandClasses[(size_t)std::get<3>(c)].G,
+                             bandClasses[(size_t)std::get<3>(c)].Q, 2 * bandClasses[(size_t)std::get<3>(c)].G * bandClasses[(size_t)std::get<3>(c)].Q,
+                             std::get<2>(c));
+            else
+                std::fprintf(stderr, "[lara_b200]   DP class full matrix R=%d: %d pairs\n", std::get<0>(c), std::get<2>(c));
+        }
     if (!wk.evFork) CK(cudaEventCreateWithFlags(&wk.evFork, cudaEventDisableTiming));
     while (wk.aux.size() + 1 < cls.size())
     {
