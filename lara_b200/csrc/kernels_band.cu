@@ -49,11 +49,7 @@ namespace
 
 constexpr unsigned kFull = 0xffffffffu;
 
-template <int Q> struct TraceUnit;
-template <> struct TraceUnit<4>  { using type = uint16_t; };
-template <> struct TraceUnit<8>  { using type = uint32_t; };
-template <> struct TraceUnit<16> { using type = uint2; };
-
+// one trace unit = the Q decision nibbles of one run: 2, 4 or 8 bytes
 template <int Q>
 __device__ __forceinline__ void store_unit(void * base, size_t unitIdx, uint32_t const (&tw)[(Q + 7) / 8])
 {

@@ -3,9 +3,11 @@
 // Drop-in seam: lara::solve(results, store, params)  (src/subgradient_solver.hpp:110, src/lara.cpp:57).
 // The reference keeps `threads` solver slots alive and refills them from a longest-first queue
 // (src/subgradient_solver.hpp:112-120, 286-325).  Here the queue becomes length-sorted BATCHES of pairs
-// that iterate in lock step; each iteration is one DP launch per rows-per-lane class plus one
-// post-processing launch.  Pairs are independent, so several GPUs simply take interleaved shares of the
-// sorted pair list (one host thread per device, no collective).
+// that iterate in lock step; each iteration is one DP launch per kernel class present in the batch (band
+// shape (G, Q) or rows per lane R, side by side on streams) plus one post-processing launch.  Several
+// workers per device pull batches from the device's queue and run them concurrently.  Pairs are independent,
+// so several GPUs simply take interleaved shares of the sorted pair list (one host thread per device, no
+// collective).
 #include "lara_gpu.cuh"
 
 #include <algorithm>

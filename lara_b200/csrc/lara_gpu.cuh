@@ -1,8 +1,10 @@
 // lara_gpu.cuh -- shared device-side definitions of the B200 LaRA hot path.
 //
 // Execution model: a batch of sequence pairs advances through the subgradient
-// iterations in lock step; every iteration is two kernel launches over the batch,
-//   1. gotoh_fill_kernel<R>   one warp per pair, the affine-gap DP over the full lenA x lenB matrix
+// iterations in lock step; every iteration is
+//   1. gotoh_band_kernel<G,Q> G lanes per pair (one thread per pair at G = 1): the affine-gap DP over the band of
+//                             diagonals that holds the pair's active edges, exact (kernels_band.cu); pairs without a
+//                             usable band: gotoh_fill_kernel<R>, one warp per pair over the full matrix (kernels_dp.cu)
 //   2. iterate_post_kernel    one warp per pair: traceback, valid_solution + greedy matching,
 //                             bounds / step size / multiplier update, pssm refresh
 // and the per-pair Lagrange problem lives in HBM in the flat layout described below.
