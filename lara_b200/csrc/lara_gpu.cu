@@ -131,13 +131,65 @@ struct lara_ctx
 namespace
 {
 
+// Page-locked host blocks for the result arrays (device-to-host copies at full PCIe / C2C speed).  Pinning is slow
+// (~0.2 ms per MB), so freed blocks are kept for the next result set of similar size.
+struct PinnedCache
+{
+    std::mutex m;
+    std::vector<std::pair<void *, size_t>> blocks;
+    void * acquire(size_t bytes, size_t & got)
+    {
+        {
+            std::lock_guard<std::mutex> lock(m);
+            for (size_t i = 0; i < blocks.size(); ++i)
+                if (blocks[i].second >= bytes && blocks[i].second <= 2 * bytes + (1u << 20))
+                {
+                    void * p = blocks[i].first;
+                    got = blocks[i].second;
+                    blocks.erase(blocks.begin() + (long)i);
+                    return p;
+                }
+        }
+        void * p = nullptr;
+        if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        got = bytes;
+        return p;
+    }
+    void release(void * p, size_t bytes)
+    {
+        std::lock_guard<std::mutex> lock(m);
+        blocks.emplace_back(p, bytes);
+        while (blocks.size() > 2) { cudaFreeHost(blocks.front().first); blocks.erase(blocks.begin()); }
+    }
+};
+PinnedCache g_pinned;
+
 struct ResultOwner
 {
     std::vector<lara_pair_result> pairs;
-    // not value-initialised: the device-to-host copies write every element
-    std::unique_ptr<int32_t[]> posLow, posHigh;
-    std::unique_ptr<uint32_t[]> weight;
+    // one block: posLow | posHigh | weight (not initialised: the device-to-host copies write every element);
+    // page-locked when possible, else plain memory
+    void * block = nullptr;
+    size_t blockBytes = 0;
+    bool pinned = false;
+    int32_t * posLow = nullptr, * posHigh = nullptr;
+    uint32_t * weight = nullptr;
     int64_t nLines = 0;
+    void allocate(int64_t n)
+    {
+        size_t const each = (size_t)std::max<int64_t>(n, 1);
+        block = g_pinned.acquire(3 * each * 4, blockBytes);
+        pinned = block != nullptr;
+        if (!block) { block = ::operator new(3 * each * 4); blockBytes = 3 * each * 4; }
+        posLow = static_cast<int32_t *>(block);
+        posHigh = posLow + each;
+        weight = reinterpret_cast<uint32_t *>(posHigh + each);
+    }
+    ~ResultOwner()
+    {
+        if (block && pinned) g_pinned.release(block, blockBytes);
+        else if (block) ::operator delete(block);
+    }
 };
 
 DevParams make_dev_params(lara_params const & P)
@@ -1108,9 +1160,7 @@ int lara_gpu_fetch_prepared(lara_ctx * ctx, lara_results * out)
         }
         int64_t const total = devBase.back();
         own->nLines = total;
-        own->posLow.reset(new int32_t[(size_t)std::max<int64_t>(total, 1)]);
-        own->posHigh.reset(new int32_t[(size_t)std::max<int64_t>(total, 1)]);
-        own->weight.reset(new uint32_t[(size_t)std::max<int64_t>(total, 1)]);
+        own->allocate(total);
         // 2. gather on the device, three dense copies per device
         double msD2h = 0;
         std::vector<int32_t *> scratch(ctx->devs.size(), nullptr);
@@ -1127,9 +1177,9 @@ int lara_gpu_fetch_prepared(lara_ctx * ctx, lara_results * out)
             CK(cudaEventRecord(dv.events[0], dv.stream));
             CK(launch_pack_lines((int)dv.pairs.size(), dv.dOutHdr, dv.dOutLines, dv.dOutOff, dDst, scratch[k], scratch[k] + nL,
                                  scratch[k] + 2 * nL, dv.stream));
-            CK(cudaMemcpyAsync(own->posLow.get() + devBase[k], scratch[k], sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
-            CK(cudaMemcpyAsync(own->posHigh.get() + devBase[k], scratch[k] + nL, sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
-            CK(cudaMemcpyAsync(own->weight.get() + devBase[k], scratch[k] + 2 * nL, sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
+            CK(cudaMemcpyAsync(own->posLow + devBase[k], scratch[k], sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
+            CK(cudaMemcpyAsync(own->posHigh + devBase[k], scratch[k] + nL, sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
+            CK(cudaMemcpyAsync(own->weight + devBase[k], scratch[k] + 2 * nL, sizeof(int32_t) * (size_t)nL, cudaMemcpyDeviceToHost, dv.stream));
             CK(cudaEventRecord(dv.events[1], dv.stream));
             CK(cudaFreeAsync(dDst, dv.stream));
             CK(cudaFreeAsync(scratch[k], dv.stream));
@@ -1169,9 +1219,9 @@ int lara_gpu_fetch_prepared(lara_ctx * ctx, lara_results * out)
     out->n_pairs = ctx->nPrepared;
     out->pairs = own->pairs.data();
     out->n_lines_total = own->nLines;
-    out->line_pos_low = own->posLow.get();
-    out->line_pos_high = own->posHigh.get();
-    out->line_weight = own->weight.get();
+    out->line_pos_low = own->posLow;
+    out->line_pos_high = own->posHigh;
+    out->line_weight = own->weight;
     out->owner_ = own;
     return LARA_OK;
 }
