@@ -15,7 +15,6 @@ namespace
 {
 
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int RF = 8;                       // rows per lane of the filter sweep (multi-pass over 256-row blocks)
 constexpr int32_t kEfNeg = -LARA_INFINITY;  // "-infinity" of src/edge_filter.hpp:81-96
 
 __device__ __forceinline__ int32_t max3(int32_t a, int32_t b, int32_t c) { return max(a, max(b, c)); }
@@ -24,15 +23,16 @@ __device__ __forceinline__ int32_t max3(int32_t a, int32_t b, int32_t c) { retur
 //   M(c,r) = P(c-1,r-1) + tab[..]                      P = max(M, X, Y)   (src/edge_filter.hpp:104-106,119-123)
 //   X(c,r) = max(M+go, X+ge, Y+go)(c, r-1)             ("matrixH", :108-110)
 //   Y(c,r) = max(M+go, X+go, Y+ge)(c-1, r)             ("matrixV", :112-114)
-// Lane k owns rows pass*256 + 8k + 1 .. + 8, sweeps the columns skewed by k; rowBuf carries the last row of
-// a 256-row block to the next pass.  kBackward: sequences reversed, and instead of storing the prefix
+// Lane k owns rows pass*32*RF + RF*k + 1 .. + RF, sweeps the columns skewed by k; rowBuf carries the last row of
+// a 32*RF-row block to the next pass (RF is chosen per launch so that the usual case is a single pass).  The 5 x 5
+// score table sits in shared memory: the lanes of a step are in different columns, i.e. read different entries.  kBackward: sequences reversed, and instead of storing the prefix
 // score the activity test of generateEdges (:146-154) is evaluated on the fly.
-template <bool kBackward>
+template <bool kBackward, int RF>
 __device__ int32_t filter_sweep(int la, int lb, uint8_t const * __restrict__ A, uint8_t const * __restrict__ B,
-                                DevParams const & P, int32_t * __restrict__ fwdP, int32_t * __restrict__ rowBuf,
-                                uint32_t * __restrict__ bits, int bitWords, int32_t threshold, int lane)
+                                int32_t go, int32_t ge, int32_t const * __restrict__ sTab, int32_t * __restrict__ fwdP,
+                                int32_t * __restrict__ rowBuf, uint32_t * __restrict__ bits, int bitWords, int32_t threshold,
+                                int lane)
 {
-    int32_t const go = P.go, ge = P.ge;
     int const nPass = (lb + 32 * RF - 1) / (32 * RF);
     int32_t optOut = 0;
     for (int pass = 0; pass < nPass; ++pass)
@@ -82,7 +82,7 @@ __device__ int32_t filter_sweep(int la, int lb, uint8_t const * __restrict__ A, 
                 for (int j = 0; j < RF; ++j)
                 {
                     int const r = rBase + j + 1;
-                    int32_t const sub = P.tab[ca * 5 + cb[j]];
+                    int32_t const sub = sTab[ca * 5 + cb[j]];
                     int32_t const m = diag + sub;
                     int32_t const x = max3(uM + go, uX + ge, uY + go);
                     int32_t const y = max3(Ml[j] + go, Xl[j] + go, Yl[j] + ge);
@@ -121,10 +121,14 @@ __device__ int32_t filter_sweep(int la, int lb, uint8_t const * __restrict__ A, 
     return optOut;
 }
 
+template <int RF>
 __global__ void __launch_bounds__(128)
 edge_filter_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ state, int32_t * __restrict__ arena,
                    DevInputs in, DevParams P)
 {
+    __shared__ int32_t sTab[25];
+    if (threadIdx.x < 25) sTab[threadIdx.x] = P.tab[threadIdx.x];
+    __syncthreads();
     int const p = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
     int const lane = threadIdx.x & 31;
     if (p >= n) return;
@@ -138,10 +142,10 @@ edge_filter_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__
     int const nWords = la * d.bitWords;
     for (int i = lane; i < nWords; i += 32) bits[i] = 0u;
     __syncwarp();
-    int32_t const opt = filter_sweep<false>(la, lb, A, B, P, fwdP, rowBuf, bits, d.bitWords, 0, lane);
+    int32_t const opt = filter_sweep<false, RF>(la, lb, A, B, P.go, P.ge, sTab, fwdP, rowBuf, bits, d.bitWords, 0, lane);
     __syncwarp();
     int32_t const threshold = opt - P.subopt;                  // src/edge_filter.hpp:142
-    filter_sweep<true>(la, lb, A, B, P, fwdP, rowBuf, bits, d.bitWords, threshold, lane);
+    filter_sweep<true, RF>(la, lb, A, B, P.go, P.ge, sTab, fwdP, rowBuf, bits, d.bitWords, threshold, lane);
     __syncwarp();
     int cnt = 0;
     for (int i = lane; i < nWords; i += 32) cnt += __popc(bits[i]);
@@ -486,10 +490,14 @@ __global__ void dense_to_stream_kernel(int n, PairDesc const * __restrict__ desc
 } // namespace
 
 cudaError_t launch_edge_filter(int n, PairDesc * desc, PairState * state, int32_t * arena, DevInputs in,
-                               DevParams const & P, cudaStream_t stream)
+                               DevParams const & P, int maxLb, cudaStream_t stream)
 {
     if (n <= 0) return cudaSuccess;
-    edge_filter_kernel<<<(n + 3) / 4, 128, 0, stream>>>(n, desc, state, arena, in, P);
+    // rows per lane: the smallest instantiation that covers the longest second sequence of the launch in one pass
+    if (maxLb <= 128) edge_filter_kernel<4><<<(n + 3) / 4, 128, 0, stream>>>(n, desc, state, arena, in, P);
+    else if (maxLb <= 256) edge_filter_kernel<8><<<(n + 3) / 4, 128, 0, stream>>>(n, desc, state, arena, in, P);
+    else if (maxLb <= 384) edge_filter_kernel<12><<<(n + 3) / 4, 128, 0, stream>>>(n, desc, state, arena, in, P);
+    else edge_filter_kernel<16><<<(n + 3) / 4, 128, 0, stream>>>(n, desc, state, arena, in, P);
     return cudaGetLastError();
 }
 

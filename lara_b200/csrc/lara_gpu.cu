@@ -392,7 +392,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     cudaEvent_t evS0 = wk.events[0], evS1 = wk.events[1];
     CK(cudaEventRecord(evS0, s));
     // ---- stage 1: edge filter -> E ------------------------------------------------------------------
-    CK(launch_edge_filter(n, dDesc, dState, arena, dv.in, dp, s));
+    CK(launch_edge_filter(n, dDesc, dState, arena, dv.in, dp, maxLb, s));
     CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     lap("edge filter (sync)");
@@ -1469,7 +1469,7 @@ int lara_gpu_edge_filter(lara_ctx * ctx, uint8_t const * seqA, int32_t lenA, uin
         CK(cudaMalloc((void **)&dState, sizeof(PairState)));
         CK(cudaMemcpyAsync(dDesc, &d, sizeof(d), cudaMemcpyHostToDevice, s));
         CK(cudaMemsetAsync(dState, 0, sizeof(PairState), s));
-        CK(launch_edge_filter(1, dDesc, dState, rg.ptr, in, ctx->dp, s));
+        CK(launch_edge_filter(1, dDesc, dState, rg.ptr, in, ctx->dp, lenB, s));
         std::vector<uint32_t> bits((size_t)lenA * d.bitWords);
         PairState hs;
         CK(cudaMemcpyAsync(bits.data(), rg.ptr + d.offBits, bits.size() * 4, cudaMemcpyDeviceToHost, s));

@@ -179,7 +179,7 @@ cudaError_t launch_pack_lines(int n, PairOutHdr const * hdr, int32_t const * out
 cudaError_t post_configure_device();
 // set-up stage 1: edge filter -> bitmap, optimum score, E
 cudaError_t launch_edge_filter(int n, PairDesc * desc, PairState * state, int32_t * arena, DevInputs in,
-                               DevParams const & P, cudaStream_t stream);
+                               DevParams const & P, int maxLb, cudaStream_t stream);
 // set-up stage 2: rowStart, cell ids, sequence scores, interaction counts -> D, stream geometry -> nVals
 cudaError_t launch_setup_count(int n, PairDesc * desc, PairState * state, int32_t * arena, DevInputs in,
                                DevParams const & P, cudaStream_t stream);
