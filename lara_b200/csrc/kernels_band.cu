@@ -49,12 +49,13 @@ namespace
 
 constexpr unsigned kFull = 0xffffffffu;
 
-// one trace unit = the Q decision nibbles of one run: 2, 4 or 8 bytes
+// one trace unit = the Q decision nibbles of one run: 2, 4 or 8 bytes (Q = 12: 8 bytes, 12 nibbles used)
 template <int Q>
 __device__ __forceinline__ void store_unit(void * base, size_t unitIdx, uint32_t const (&tw)[(Q + 7) / 8])
 {
     if constexpr (Q == 4) reinterpret_cast<uint16_t *>(base)[unitIdx] = (uint16_t)(tw[0] >> 16);
     else if constexpr (Q == 8) reinterpret_cast<uint32_t *>(base)[unitIdx] = tw[0];
+    else if constexpr (Q == 12) reinterpret_cast<uint2 *>(base)[unitIdx] = make_uint2(tw[0], tw[1] >> 16);   // 12 of 16 nibbles
     else reinterpret_cast<uint2 *>(base)[unitIdx] = make_uint2(tw[0], tw[1]);
 }
 
@@ -320,6 +321,7 @@ cudaError_t launch_compact_slots(int n, int32_t const * in, PairState const * st
 bool band_shape_supported(int G, int Q)
 {
     if (Q == 16) return G == 1 || G == 2 || G == 4 || G == 8 || G == 16 || G == 32;
+    if (Q == 12) return G == 1;
     if (Q == 8) return G == 2 || G == 4 || G == 8 || G == 16 || G == 32;
     if (Q == 4) return G == 4 || G == 8 || G == 16 || G == 32;
     return false;
@@ -332,6 +334,7 @@ cudaError_t launch_gotoh_band(int G, int Q, int nSlots, int32_t const * pairIdx,
         return cudaSuccess;
 #define LARA_GQ(g_, q_) if (G == g_ && Q == q_) return launch_gq<g_, q_>(nSlots, pairIdx, desc, state, arena, go, ge, stream);
     LARA_GQ(1, 16) LARA_GQ(2, 16) LARA_GQ(4, 16) LARA_GQ(8, 16) LARA_GQ(16, 16) LARA_GQ(32, 16)
+    LARA_GQ(1, 12)
     LARA_GQ(2, 8) LARA_GQ(4, 8) LARA_GQ(8, 8) LARA_GQ(16, 8) LARA_GQ(32, 8)
     LARA_GQ(4, 4) LARA_GQ(8, 4) LARA_GQ(16, 4) LARA_GQ(32, 4)
 #undef LARA_GQ

@@ -354,6 +354,13 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
                     uint2 const u0 = __ldg(src), u1 = __ldg(src + v.ppw);
                     w[0] = u0.x; w[1] = u0.y; w[2] = u1.x; w[3] = u1.y;
                 }
+                else if (v.Q == 12)
+                {
+                    // two units of 12 nibbles in 8 bytes each (band of 24 diagonals, xLo == 0)
+                    uint2 const * __restrict__ src = reinterpret_cast<uint2 const *>(v.trace) + ((size_t)rr * nUnits) * v.ppw + v.slot;
+                    uint2 const u0 = __ldg(src), u1 = __ldg(src + v.ppw);
+                    w[0] = u0.x; w[1] = (u0.y & 0xffffu) | (u1.x << 16); w[2] = (u1.x >> 16) | (u1.y << 16); w[3] = 0u;
+                }
                 else if (v.Q == 8)
                 {
                     // units of 8 nibbles (one word)

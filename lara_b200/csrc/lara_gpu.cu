@@ -113,6 +113,7 @@ struct lara_ctx
     int bandMargin = 1;                     // diagonals added on both sides of the active range (env LARA_B200_MARGIN)
     int bandMaxW = 1024;                    // widest band; beyond it the full-matrix kernel runs (env LARA_B200_BANDMAXW)
     int bandMinWarps = 400;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
+    bool band24 = true;                     // 24-diagonal one-thread-per-pair shape (env LARA_B200_BAND24=0: off)
     int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
     int verbose = 0;                        // env LARA_B200_VERBOSE=1: host-side stage times of every batch on stderr
     bool compactSlots = false;              // repack the DP slot lists as pairs finish (env LARA_B200_COMPACT=1); measured:
@@ -250,7 +251,7 @@ double ev_ms(cudaEvent_t a, cudaEvent_t b)
 // Band geometry of one pair from the diagonal range of its active edges (kernels_band.cu): dLo <= 0 <= dHi,
 // bandW = 32 .. 1024 diagonals (multiple of 32).  bandW = 0 selects the full-matrix kernel (band wider than 1024
 // diagonals, or gap costs outside the band kernel's precondition go < ge).
-void choose_band(lara_ctx const & ctx, PairDesc & d)
+void choose_band(lara_ctx const & ctx, PairDesc & d, bool allow24)
 {
     d.bandW = 0; d.bandG = 0; d.bandQ = 0; d.bandSlot = 0; d.dLo = 0; d.dHi = -1;
     if (!ctx.bandMode || !(ctx.dp.go < ctx.dp.ge)) return;
@@ -261,7 +262,7 @@ void choose_band(lara_ctx const & ctx, PairDesc & d)
         hi = std::max(d.dMax + ctx.bandMargin, 0);
     }
     int const need = hi - lo + 1;
-    int W = 32;
+    int W = (allow24 && need <= 24) ? 24 : 32;
     while (W < need) W <<= 1;
     if (W > ctx.bandMaxW) return;
     // a band that needs the full-matrix kernel's work or more is not worth it (short sequences)
@@ -276,6 +277,7 @@ void choose_band(lara_ctx const & ctx, PairDesc & d)
 // else Q = 4 (G = W / 8).
 void choose_band_shape(lara_ctx const & ctx, int W, int nPairs, int & G, int & Q)
 {
+    if (W == 24) { G = 1; Q = 12; return; }                     // one thread per pair only
     int const g16 = W / 32, g8 = W / 16, g4 = W / 8;
     int64_t const warps16 = ((int64_t)nPairs * g16 + 31) / 32, warps8 = ((int64_t)nPairs * g8 + 31) / 32;
     Q = (g8 > 32 || warps16 >= ctx.bandMinWarps) ? 16 : ((g4 > 32 || warps8 >= ctx.bandMinWarps) ? 8 : 4);
@@ -399,10 +401,38 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     wk.stats.kernel_launches += 1;
     // ---- stage B layout: per-edge arrays, band geometry and warp groups of the band kernels --------------------
     std::map<int, std::vector<int32_t>> byW;               // band width -> pairs
+    // the 24-diagonal shape exists as one thread per pair only: used when enough pairs of the batch fit it
+    bool allow24 = false;
+    if (ctx.band24)
+    {
+        int64_t fit = 0;
+        for (int i = 0; i < n; ++i)
+        {
+            choose_band(ctx, desc[(size_t)i], true);
+            fit += desc[(size_t)i].bandW == 24;
+        }
+        allow24 = (fit + 31) / 32 >= ctx.bandMinWarps && ctx.bandForceQ == 0;
+    }
     for (int i = 0; i < n; ++i)
     {
-        choose_band(ctx, desc[(size_t)i]);
+        choose_band(ctx, desc[(size_t)i], allow24);
         if (desc[(size_t)i].bandW > 0) byW[desc[(size_t)i].bandW].push_back(i);
+    }
+    if (ctx.verbose)
+    {
+        int hist[9] = {0}, fine[4] = {0};
+        for (int i = 0; i < n; ++i)
+        {
+            PairDesc const & d = desc[(size_t)i];
+            int const need = (d.E > 0 && d.dMin <= d.dMax) ? std::max(d.dMax + ctx.bandMargin, 0) - std::min(d.dMin - ctx.bandMargin, 0) + 1 : 1;
+            int b = 0;
+            while (b < 8 && (8 << b) < need) ++b;
+            ++hist[b];
+            if (need > 16 && need <= 32) ++fine[(need - 17) / 4];
+        }
+        std::fprintf(stderr, "[lara_b200]   band need histogram (<=8,16,32,64,128,256,512,1024,more):");
+        for (int b = 0; b < 9; ++b) std::fprintf(stderr, " %d", hist[b]);
+        std::fprintf(stderr, "; 17-20 21-24 25-28 29-32: %d %d %d %d\n", fine[0], fine[1], fine[2], fine[3]);
     }
     struct BandClass { int G, Q; std::vector<int32_t> slots; };    // slots: pair index or -1, 32 / G per warp group
     std::vector<BandClass> bandClasses;
@@ -453,7 +483,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         }
     }
     for (BandGroup const & g : groups)
-        sizeB += align4((int64_t)g.rows * g.W * g.ppw) + align4((int64_t)g.rows * (g.W / 8) * g.ppw) +
+        sizeB += align4((int64_t)g.rows * g.W * g.ppw) + align4((int64_t)g.rows * (g.W == 24 ? 4 : g.W / 8) * g.ppw) +
                  4ll * g.ppw * (g.rows + g.cols);
     lap("layout B (host)");
     Region rB;
@@ -485,7 +515,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     for (BandGroup const & g : groups)
     {
         int64_t const ov = rB.take((int64_t)g.rows * g.W * g.ppw);
-        int64_t const ot = rB.take((int64_t)g.rows * (g.W / 8) * g.ppw);
+        int64_t const ot = rB.take((int64_t)g.rows * (g.W == 24 ? 4 : g.W / 8) * g.ppw);   // W = 24: 2 units of 8 bytes per row
         int64_t const ou = rB.take(4ll * g.ppw * g.rows);
         int64_t const ol = rB.take(4ll * g.ppw * g.cols);
         for (int j = 0; j < g.count; ++j)
@@ -876,6 +906,7 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_MARGIN")) ctx->bandMargin = std::max(0, std::min(16, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BANDMAXW")) ctx->bandMaxW = std::max(0, std::min(1024, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BANDMINWARPS")) ctx->bandMinWarps = std::max(1, std::atoi(e));
+    if (char const * e = std::getenv("LARA_B200_BAND24")) ctx->band24 = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_BANDQ")) ctx->bandForceQ = std::atoi(e);
     if (char const * e = std::getenv("LARA_B200_VERBOSE")) ctx->verbose = std::atoi(e);
     if (char const * e = std::getenv("LARA_B200_COMPACT")) ctx->compactSlots = std::atoi(e) != 0;
@@ -1344,10 +1375,10 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
                               int32_t * score, int32_t * n_lines, int32_t * lines_a, int32_t * lines_b, int32_t * gap_score)
 {
     if (!ctx || !pssm || n_problems < 1 || lenA < 1 || lenB < 1) return set_err(ctx, LARA_E_INVALID, "bad argument");
-    int const G = lanes, W = band_width, Q = (G > 0 && W % (2 * G) == 0) ? W / (2 * G) : 0;
+    int const G = lanes, W = band_width, Q = (G > 0 && W % (2 * G) == 0) ? W / (2 * G) : 0;     // (24, 1) -> Q = 12
     if (!band_shape_supported(G, Q) || d_lo > 0 || d_lo + W - 1 < 0)
         return set_err(ctx, LARA_E_INVALID, "band: width / (2 * lanes) must be 16 (lanes 1..32), 8 (lanes 2..32) or 4 (lanes 4..32), "
-                                            "and d_lo <= 0 <= d_lo + width - 1");
+                                            "or 12 (width 24, one lane), and d_lo <= 0 <= d_lo + width - 1");
     if (!(gap_open < gap_extend)) return set_err(ctx, LARA_E_UNSUPPORTED, "band kernel needs gap_open < gap_extend");
     Device & dv = ctx->devs[0];
     cudaStream_t const s = dv.stream;
@@ -1365,7 +1396,7 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
             for (int gi = 0; gi < nGroups; ++gi)
             {
                 int64_t const ov = rg.take((int64_t)(lenB + 1) * W * ppw);
-                int64_t const ot = rg.take((int64_t)(lenB + 1) * (W / 8) * ppw);
+                int64_t const ot = rg.take((int64_t)(lenB + 1) * (W == 24 ? 4 : W / 8) * ppw);
                 int64_t const ou = rg.take(4ll * ppw * (lenB + 1));
                 int64_t const ol = rg.take(4ll * ppw * (lenA + 1));
                 for (int j = 0; j < ppw && gi * ppw + j < n; ++j)

@@ -86,7 +86,7 @@ struct PairDesc
     int64_t offScratch;         // set-up scratch: forward prefix scores [la * lb]
     // ---- band mode (kernels_band.cu): the DP runs only over the diagonals dLo <= c - r <= dHi ------------
     int32_t dMin, dMax;         // diagonal range (a - b) of the active edges (edge filter); dMin > dMax: none
-    int32_t bandW;              // diagonals of the band = 2 * bandG * bandQ (multiple of 32); 0 = full-matrix kernel
+    int32_t bandW;              // diagonals of the band = 2 * bandG * bandQ (24 or a multiple of 32); 0 = full-matrix kernel
     int32_t bandG, bandQ;       // lanes per pair (32 / bandG pairs share a warp) and diagonals per block
     int32_t bandSlot;           // position of the pair inside its warp group: 0 .. 32 / bandG - 1
     int32_t dLo, dHi;           // band (dLo <= 0 <= dHi, dHi = dLo + bandW - 1)

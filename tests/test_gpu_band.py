@@ -13,7 +13,7 @@ INIT = -1431655764
 
 # (band width, lanes per problem)
 SHAPES = [(32, 1), (64, 2), (128, 4), (256, 8), (512, 16), (1024, 32), (32, 4), (64, 8), (128, 16), (256, 32),
-          (32, 2), (64, 4), (128, 8), (256, 16), (512, 32)]
+          (32, 2), (64, 4), (128, 8), (256, 16), (512, 32), (24, 1)]
 
 
 def band_pssm(rng, n, la, lb, d_lo, d_hi, density, alphabet=None):
@@ -58,7 +58,7 @@ def test_band_random(gpu_ctx_factory, la, lb, frac, width, lanes):
         check(ctx, band_pssm(rng, n, la, lb, d_lo, d_hi, density), d_lo, width, lanes)
 
 
-@pytest.mark.parametrize("width,lanes", [(32, 1), (32, 2), (32, 4), (64, 2), (64, 8)])
+@pytest.mark.parametrize("width,lanes", [(32, 1), (24, 1), (32, 2), (32, 4), (64, 2), (64, 8)])
 @pytest.mark.parametrize("la,lb,d_lo", [(12, 12, -4), (70, 50, -10), (150, 140, -8), (90, 90, -20)])
 def test_band_ties(gpu_ctx_factory, la, lb, d_lo, width, lanes):
     """Small score alphabet: masses of ties, inside the band and against the closed-form regions."""
@@ -71,11 +71,13 @@ def test_band_ties(gpu_ctx_factory, la, lb, d_lo, width, lanes):
     check(ctx, p, d_lo, width, lanes, go=-3 * 8192, ge=-1 * 8192)
 
 
-@pytest.mark.parametrize("width,lanes", [(32, 1), (32, 2), (32, 4), (64, 2), (64, 8)])
+@pytest.mark.parametrize("width,lanes", [(32, 1), (24, 1), (32, 2), (32, 4), (64, 2), (64, 8)])
 @pytest.mark.parametrize("la,lb,d_lo", [(200, 60, 0), (200, 60, -6), (400, 100, -2), (120, 119, 0), (90, 80, -31)])
 def test_band_end_cell_outside_and_escapes(gpu_ctx_factory, la, lb, d_lo, width, lanes):
     """la - lb beyond the band: the end cell and the start of the traceback lie in region U; d_lo = 0 pushes
-    vertical detours into region L; d_lo = -31 puts the main diagonal at the band's upper edge."""
+    vertical detours into region L; d_lo = -31 stands for "main diagonal at the band's upper edge"."""
+    if d_lo == -31:
+        d_lo = -(width - 1)
     ctx, _ = gpu_ctx_factory()
     rng = np.random.default_rng(la + 3 * lb + d_lo)
     d_hi = d_lo + width - 1

@@ -97,6 +97,8 @@ def test_solve_skewed_lengths(built):
     dict(LARA_B200_BANDQ="16"),
     dict(LARA_B200_BANDQ="16", LARA_B200_COMPACT="1", LARA_B200_BATCH="40", LARA_B200_WORKERS="3"),
     dict(LARA_B200_BANDMAXW="32", LARA_B200_BATCH="33"),
+    dict(LARA_B200_BANDMINWARPS="1"),                   # lets the 24-diagonal one-thread shape in on a small batch
+    dict(LARA_B200_BAND24="0", LARA_B200_BANDMINWARPS="1"),
 ])
 def test_solve_kernel_variants(built, env, monkeypatch):
     """Every DP kernel family and the scheduling switches give the same bits: full matrix, band blocks of 4 / 8 / 16
