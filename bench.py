@@ -348,17 +348,26 @@ def main():
     int_rates = {k: ctx.int_issue_rate(k) for k in (0, 1, 2)}
     iso = None
     if not multi_proc and args.gpus == 1 and not args.no_isolated:
+        prev_workers = os.environ.get("LARA_B200_WORKERS")
         os.environ["LARA_B200_WORKERS"] = "1"
-        ctx1 = lb.Context(params, device_ids=device_ids)
-        os.environ.pop("LARA_B200_WORKERS", None)
-        ctx1.set_sequences(flat)
-        ctx1.prepare_pairs(my_a, my_b)
-        ctx1.run_prepared()
-        s1 = ctx1.stats()
-        iso = {"dp_ms": s1.ms_dp, "post_ms": s1.ms_bounds, "setup_ms": s1.ms_setup, "device_ms": s1.ms_device,
-               "dp_launches": s1.dp_launches, "dp_bytes": s1.reserved[4], "dp_cells_band": s1.reserved[5],
-               "dp_cells": s1.dp_cells}
-        ctx1.close()
+        try:
+            ctx1 = lb.Context(params, device_ids=device_ids)
+            ctx1.set_sequences(flat)
+            ctx1.prepare_pairs(my_a, my_b)
+            ctx1.run_prepared()
+            s1 = ctx1.stats()
+            iso = {"dp_ms": s1.ms_dp, "post_ms": s1.ms_bounds, "setup_ms": s1.ms_setup, "device_ms": s1.ms_device,
+                   "dp_launches": s1.dp_launches, "dp_bytes": s1.reserved[4], "dp_cells_band": s1.reserved[5],
+                   "dp_cells": s1.dp_cells}
+            ctx1.close()
+        except Exception as ex:          # the extra pass is informative only; the timed region above stands
+            log("isolated roofline pass failed: %r" % (ex,))
+            iso = None
+        finally:
+            if prev_workers is None:
+                os.environ.pop("LARA_B200_WORKERS", None)
+            else:
+                os.environ["LARA_B200_WORKERS"] = prev_workers
     achieved = dp_bytes / (dp_ms * 1e-3) / 1e9 if dp_ms > 0 else 0.0
     roofline = {
         "kernel": "gotoh_band_kernel", "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",

@@ -725,7 +725,11 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers, doub
 {
     size_t freeB = 0, totalB = 0;
     cudaMemGetInfo(&freeB, &totalB);
-    double const budget = 0.55 * (double)totalB / (double)nWorkers;
+    // what this device's workers may use together: 55 % of the device, but not more than what is free now plus the
+    // slabs they already hold (other contexts or processes may live on the same device)
+    double held = 0;
+    for (Worker const & w : dv.workers) held += 4.0 * (double)w.slabInts;
+    double const budget = std::min(0.55 * (double)totalB, 0.9 * ((double)freeB + held)) / (double)nWorkers;
     double used = 0;
     size_t k = begin;
     size_t hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : ctx.batchPairsDefault;
