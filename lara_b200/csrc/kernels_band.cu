@@ -38,7 +38,9 @@
 //
 // Memory: position specific scores come from a dense band array vals[row][diagonal], stored in 16-byte chunks of 4
 // diagonals and interleaved over the pairs of a warp ([row][chunk][pair slot]) so that a warp-wide 128-bit load is
-// contiguous; four decision bits per cell go to trace units of Q nibbles ([row][block][pair slot]).
+// contiguous; four decision bits per cell go to trace units of Q nibbles ([row][block][pair slot]).  One thread per
+// pair (G = 1): the two units of a row are written as one 16-byte record and two rows share a 32-byte sector
+// ([row / 2][pair slot][row % 2]), because the traceback reads a single pair's rows and pays per sector.
 #include "lara_gpu.cuh"
 
 namespace lara
@@ -175,6 +177,7 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
     if (1 - g >= 1 && 1 - g <= lb) load_run(subA, 1 - g, 2 * g);
 
     int const nIter = lbMax + G;
+    uint32_t twA[2] = {0u, 0u};                                     // G == 1: block A's unit waits for block B's
     for (int i = 0; i < nIter; ++i)
     {
         int const r = i - g + 1;
@@ -218,7 +221,8 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
                     HA = band_run<Q, true>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, tw, jEnd, sE, vE, hE);
                 else
                     HA = band_run<Q, false>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, tw, 0, sE, vE, hE);
-                store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g)) * PPW + gs, tw);
+                if constexpr (G == 1) { twA[0] = tw[0]; twA[1] = tw[TW - 1]; }
+                else store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g)) * PPW + gs, tw);
             }
         }
         if (r + 1 >= 1 && r + 1 <= lb) load_run(subA, r + 1, 2 * g);
@@ -251,7 +255,14 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
                     HB = band_run<Q, true>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, tw, jEnd, sE, vE, hE);
                 else
                     HB = band_run<Q, false>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, tw, 0, sE, vE, hE);
-                store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g + 1)) * PPW + gs, tw);
+                if constexpr (G == 1)
+                {
+                    static_assert(G != 1 || TW == 2, "one thread per pair: units of 8 bytes");
+                    uint4 const rec = (Q == 12) ? make_uint4(twA[0], twA[1] >> 16, tw[0], tw[TW - 1] >> 16)
+                                                : make_uint4(twA[0], twA[1], tw[0], tw[TW - 1]);
+                    reinterpret_cast<uint4 *>(trace)[(((size_t)(r >> 1) * PPW + gs) << 1) + (r & 1)] = rec;
+                }
+                else store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g + 1)) * PPW + gs, tw);
             }
         }
     }

@@ -23,6 +23,7 @@ namespace
 {
 
 constexpr unsigned kFull = 0xffffffffu;
+
 constexpr int kMaxLookahead = 8;
 
 // pair slots (x,y), x<y<8 in lexicographic order == order of the reference's conflicts vector
@@ -346,20 +347,20 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             uint32_t w[4] = {0u, 0u, 0u, 0u};
             if (rr >= 1)
             {
-                if (v.Q == 16)
+                if (v.ppw == 32)
+                {
+                    // one thread per pair (Q = 16 or 12): 16-byte row records, two rows per sector
+                    uint4 const u = __ldg(reinterpret_cast<uint4 const *>(v.trace) + ((((size_t)(rr >> 1) * 32 + v.slot) << 1) + (rr & 1)));
+                    if (v.Q == 16) { w[0] = u.x; w[1] = u.y; w[2] = u.z; w[3] = u.w; }
+                    else { w[0] = u.x; w[1] = (u.y & 0xffffu) | (u.z << 16); w[2] = (u.z >> 16) | (u.w << 16); w[3] = 0u; }
+                }
+                else if (v.Q == 16)
                 {
                     // units of 16 nibbles (8 bytes); xLo is a multiple of 16
                     uint2 const * __restrict__ src = reinterpret_cast<uint2 const *>(v.trace) +
                                                      ((size_t)rr * nUnits + (xLo >> 4)) * v.ppw + v.slot;
                     uint2 const u0 = __ldg(src), u1 = __ldg(src + v.ppw);
                     w[0] = u0.x; w[1] = u0.y; w[2] = u1.x; w[3] = u1.y;
-                }
-                else if (v.Q == 12)
-                {
-                    // two units of 12 nibbles in 8 bytes each (band of 24 diagonals, xLo == 0)
-                    uint2 const * __restrict__ src = reinterpret_cast<uint2 const *>(v.trace) + ((size_t)rr * nUnits) * v.ppw + v.slot;
-                    uint2 const u0 = __ldg(src), u1 = __ldg(src + v.ppw);
-                    w[0] = u0.x; w[1] = (u0.y & 0xffffu) | (u1.x << 16); w[2] = (u1.x >> 16) | (u1.y << 16); w[3] = 0u;
                 }
                 else if (v.Q == 8)
                 {
@@ -612,6 +613,14 @@ __device__ int32_t greedy_matching(unsigned long long const * keys, int K, int l
 
 __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b)
 {
+    if (d.offRowRec)
+    {
+        // narrow band: the row's active cells fit one word, stored next to the id of the row's first edge
+        int2 const rec = __ldg(reinterpret_cast<int2 const *>(arena + d.offRowRec) + a);
+        int const k = b - (a - d.dHi);
+        if (k < 0 || k > 31 || !(((uint32_t)rec.y >> k) & 1u)) return -1;
+        return rec.x + __popc((uint32_t)rec.y & ((1u << k) - 1u));
+    }
     uint32_t const * bits = (uint32_t const *)(arena + d.offBits) + (size_t)a * d.bitWords;
     int e = arena[d.offRowStart + a];
     int const wb = b >> 5;
@@ -623,8 +632,10 @@ __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __res
     return e + __popc(word & ((1u << (b & 31)) - 1u));
 }
 
+// 80 registers (6 x 128 threads): with one-warp blocks 24 pairs per SM.  More pairs per SM (72 or 64 registers, or
+// more shared memory at the cost of L1) measured slower, fewer (90 registers, what ptxas takes unbounded) too.
 template <bool kTracebackOnly>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 6)
 iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
                     int32_t * __restrict__ arena, DevParams P, PairOutHdr * __restrict__ outHdr,
                     int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,

@@ -267,7 +267,19 @@ setup_count_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__
             for (int w = 0; w < bitWords; ++w) c += __popc(bits[(size_t)a * bitWords + w]);
         int total;
         int const ex = warp_excl_scan(c, lane, total);
-        if (a < la) rowStart[a] = carry + ex;
+        if (a < la)
+        {
+            rowStart[a] = carry + ex;
+            if (d.offRowRec)
+            {
+                // the row's window of the band as one word (kernels_post.cu: edge_of)
+                int const lo = a - d.dHi;
+                uint32_t word = 0u;
+                if (lo >= 0) word = strip_bits(bits + (size_t)a * bitWords, bitWords, lo, 32);
+                else if (lo > -32) word = strip_bits(bits + (size_t)a * bitWords, bitWords, 0, 32) << (-lo);
+                reinterpret_cast<int2 *>(arena + d.offRowRec)[a] = make_int2(carry + ex, (int)word);
+            }
+        }
         carry += total;
     }
     if (lane == 0) rowStart[la] = carry;

@@ -473,6 +473,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     {
         PairDesc & d = desc[(size_t)i];
         sizeB += 8 * align4(std::max(d.E, 1)) + align4(d.E + 1);
+        if (d.bandW > 0 && d.bandW <= 32) sizeB += align4(2ll * d.la);
         if (d.bandW == 0)
         {
             if (d.R > kMaxR)
@@ -483,7 +484,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         }
     }
     for (BandGroup const & g : groups)
-        sizeB += align4((int64_t)g.rows * g.W * g.ppw) + align4((int64_t)g.rows * (g.W == 24 ? 4 : g.W / 8) * g.ppw) +
+        sizeB += align4((int64_t)g.rows * g.W * g.ppw) + (g.ppw == 32 ? (int64_t)((g.rows + 1) & ~1) * 128 + 8 : align4((int64_t)g.rows * (g.W / 8) * g.ppw)) +
                  4ll * g.ppw * (g.rows + g.cols);
     lap("layout B (host)");
     Region rB;
@@ -496,6 +497,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         d.offCell = rB.take(d.E); d.offSeqScore = rB.take(d.E); d.offPv = rB.take(d.E); d.offPerm = rB.take(d.E);
         d.offIoff = rB.take(d.E + 1);
         d.offEdge = rB.take(4ll * d.E);
+        if (d.bandW > 0 && d.bandW <= 32) d.offRowRec = rB.take(2ll * d.la);
         if (d.bandW > 0)
         {
             if (!pilot)
@@ -515,7 +517,11 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     for (BandGroup const & g : groups)
     {
         int64_t const ov = rB.take((int64_t)g.rows * g.W * g.ppw);
-        int64_t const ot = rB.take((int64_t)g.rows * (g.W == 24 ? 4 : g.W / 8) * g.ppw);   // W = 24: 2 units of 8 bytes per row
+        // trace: W / 8 ints per row and pair; one thread per pair (ppw 32, W 32 or 24): 16-byte row records, two
+        // rows per 32-byte sector
+        if (g.ppw == 32) rB.used = (rB.used + 7) & ~(int64_t)7;
+        int64_t const ot = g.ppw == 32 ? rB.take((int64_t)((g.rows + 1) & ~1) * 4 * 32)
+                                       : rB.take((int64_t)g.rows * (g.W / 8) * g.ppw);
         int64_t const ou = rB.take(4ll * g.ppw * g.rows);
         int64_t const ol = rB.take(4ll * g.ppw * g.cols);
         for (int j = 0; j < g.count; ++j)
@@ -1400,7 +1406,9 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
             for (int gi = 0; gi < nGroups; ++gi)
             {
                 int64_t const ov = rg.take((int64_t)(lenB + 1) * W * ppw);
-                int64_t const ot = rg.take((int64_t)(lenB + 1) * (W == 24 ? 4 : W / 8) * ppw);
+                if (ppw == 32) rg.used = (rg.used + 7) & ~(int64_t)7;
+                int64_t const ot = ppw == 32 ? rg.take((int64_t)((lenB + 2) & ~1) * 4 * 32)
+                                             : rg.take((int64_t)(lenB + 1) * (W / 8) * ppw);
                 int64_t const ou = rg.take(4ll * ppw * (lenB + 1));
                 int64_t const ol = rg.take(4ll * ppw * (lenA + 1));
                 for (int j = 0; j < ppw && gi * ppw + j < n; ++j)

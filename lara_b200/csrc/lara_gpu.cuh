@@ -80,6 +80,8 @@ struct PairDesc
     int64_t offEdge;            // per edge, 16 bytes: { seqScore, pv (queue top == pssm value), ioff, degree }   [E]
     int64_t offInter;           // per interaction, 32 bytes: { partner edge, partner cell, structScore, dual,
                                 //                               reverse index, seqScore of the partner, owner edge, 0 }  [D]
+    int64_t offRowRec;          // bands of <= 32 diagonals, per row a of the bitmap, 8 bytes: { id of the row's first edge,
+                                //   activity bits of b = a - dHi .. a - dHi + 31 }   [la]   (0: not present)
     int64_t offLines;           // current lines  (a << 16) | b  [lb]
     int64_t offBest;            // best lines     (a << 16) | b | matched << 31  [lb]
     int64_t offCand;            // global candidate buffer for the matching sort, 2 words each [2 * kCap] (8-byte aligned)
