@@ -85,7 +85,7 @@ struct WarpSmem
     int32_t * curE;         // [maxLb]  compact edge id per line (alignment order)
     uint8_t * matched;      // [maxLb]
     unsigned long long * cand;  // [smemCand]
-    int32_t * misc;         // [16]: 0 nList, 1 nCand, 2 matchScore, 3..10 selection weights, 11 error
+    int32_t * misc;         // [32]: 0 nList, 1 nCand, 2 matchScore, 3..10 selection weights, 11 error, 16..23 selection
     uint32_t * win;         // [256] traceback window (full mode: 32 rows x 32 nibbles; band mode: 8 word rows x L)
 };
 
@@ -507,21 +507,18 @@ __device__ __forceinline__ int32_t warp_max(int32_t v)
     return v;
 }
 
-// bitonic sort of P (power of two) 64-bit keys by one warp
+// bitonic sort of P (power of two, >= 64 or == 32) 64-bit keys by one warp; every lane owns one compare-exchange per turn
 __device__ void warp_bitonic_sort(unsigned long long * buf, int P, int lane)
 {
     for (int k = 2; k <= P; k <<= 1)
         for (int j = k >> 1; j > 0; j >>= 1)
         {
-            for (int i = lane; i < P; i += 32)
+            for (int t = lane; t < (P >> 1); t += 32)
             {
-                int const ixj = i ^ j;
-                if (ixj > i)
-                {
-                    unsigned long long a = buf[i], b = buf[ixj];
-                    bool const asc = (i & k) == 0;
-                    if ((a > b) == asc) { buf[i] = b; buf[ixj] = a; }
-                }
+                int const i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), ixj = i | j;
+                unsigned long long const a = buf[i], b = buf[ixj];
+                bool const asc = (i & k) == 0;
+                if ((a > b) == asc) { buf[i] = b; buf[ixj] = a; }
             }
             __syncwarp();
         }
@@ -555,14 +552,17 @@ __device__ int32_t greedy_matching(unsigned long long const * keys, int K, int l
             unsigned const bal = __ballot_sync(kFull, ok);
             int const have = __popc(bal), need = L - ns;
             int const take = min(have, need);
-            if (lane >= ns && lane < ns + take)
-                mySel = pos + (int)__fns(bal, 0, lane - ns + 1);
+            // the lane of the k-th unmatched candidate hands it to selection slot ns + k
+            int const rank = __popc(bal & ((1u << lane) - 1u));
+            if (ok && rank < take) misc[16 + ns + rank] = i;
             if (have >= need)
-                pos = pos + (int)__fns(bal, 0, need) + 1;
+                pos = pos + __ffs(__ballot_sync(kFull, ok && rank == need - 1));
             else
                 pos = min(pos + 32, K);
             ns += take;
         }
+        __syncwarp();
+        if (lane < ns) mySel = misc[16 + lane];
         // my selected interaction
         int32_t w = 0;
         int il = -1, ir = -2;
@@ -605,10 +605,10 @@ __device__ int32_t greedy_matching(unsigned long long const * keys, int K, int l
             matched[ir] = 1;
             add = w;
         }
-        score += warp_sum(add);
+        score += add;
         __syncwarp();
     }
-    return score;
+    return warp_sum(score);
 }
 
 __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b)
@@ -655,11 +655,11 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     // carve the per-warp shared memory
     size_t const candBytes = (size_t)smemCand * 8;
     size_t const lb4 = ((size_t)maxLb * 4 + 15) / 16 * 16;
-    size_t const perWarp = candBytes + 64 + 1024 + 2 * lb4 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    size_t const perWarp = candBytes + 128 + 1024 + 2 * lb4 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
     unsigned char * base = smemRaw + (size_t)warpInBlock * perWarp;
     WarpSmem sm;
     sm.cand = (unsigned long long *)base;                     base += candBytes;
-    sm.misc = (int32_t *)base;                                base += 64;
+    sm.misc = (int32_t *)base;                                base += 128;
     sm.win = (uint32_t *)base;                                base += 1024;
     sm.linesRev = (uint32_t *)base;                           base += lb4;
     sm.curE = (int32_t *)base;                                base += lb4;
@@ -994,7 +994,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
 size_t post_smem_per_warp(int maxLa, int maxLb, int smemCand)
 {
-    return (size_t)smemCand * 8 + 64 + 1024 + 2 * (((size_t)maxLb * 4 + 15) / 16 * 16) + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    return (size_t)smemCand * 8 + 128 + 1024 + 2 * (((size_t)maxLb * 4 + 15) / 16 * 16) + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
 }
 
 } // namespace
