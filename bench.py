@@ -205,6 +205,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-isolated", action="store_true", help="skip the extra single-worker step of the roofline")
+    ap.add_argument("--emulate-world", type=int, default=0,
+                    help="developer switch: run only shard 0 of K of the pair list on this GPU (the work one rank of a "
+                         "K-GPU run does); value and gcups then count that shard only")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -260,8 +263,10 @@ def main():
     # length-sorted (longest first) global order, dealt round-robin to the ranks
     order = partition.cost_order(lens, ia, ib)
     mine = partition.shard(order, rank, world) if multi_proc else order
+    if args.emulate_world > 1 and not multi_proc:
+        mine = partition.shard(order, 0, args.emulate_world)
     my_a, my_b = ia[mine].astype(np.int32), ib[mine].astype(np.int32)
-    n_pairs_total = len(ia)
+    n_pairs_total = len(mine) if (args.emulate_world > 1 and not multi_proc) else len(ia)
 
     params = lb.Parameters()
     ctx = lb.Context(params, device_ids=device_ids)
@@ -440,7 +445,8 @@ def main():
         "metric": "aligned pairs/s", "value": value, "unit": "pairs/s", "n_gpus": max(world, args.gpus),
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-        "config": workload_config(args, w, max(world, args.gpus)),
+        "config": dict(workload_config(args, w, max(world, args.gpus)),
+                       **({"emulate_world": args.emulate_world, "pairs_run": n_pairs_total} if args.emulate_world > 1 else {})),
         "gcups": cells_all / (t_ms * 1e-3) / 1e9, "wall_ms_per_step": wall_ms / args.steps,
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches_all, "roofline": roofline, "cpu_baseline": cpu,
     }

@@ -639,7 +639,7 @@ __global__ void __launch_bounds__(128, 6)
 iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
                     int32_t * __restrict__ arena, DevParams P, PairOutHdr * __restrict__ outHdr,
                     int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
-                    int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand)
+                    int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand, int tune)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     int const warpInBlock = threadIdx.x >> 5;
@@ -668,6 +668,13 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
     int const la = d.la, lb = d.lb;
     (void)lb;
+    if (d.offRowRec && !(tune & 4))
+    {
+        // the row records of the edge lookup (step 2; 8 bytes per row): into L2 while the traceback runs
+        int2 const * rr = reinterpret_cast<int2 const *>(arena + d.offRowRec);
+        for (int a = 4 * lane; a < la; a += 128)
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(rr + a));
+    }
 
     // ---- 1. traceback + evaluateLines ------------------------------------------------------------
     int32_t gapScore = 0;
@@ -680,6 +687,14 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         bv.trace = reinterpret_cast<uint16_t const *>(arena + d.offBTrace);
         bv.uRec = reinterpret_cast<int4 const *>(arena + d.offU) + d.bandSlot;
         bv.lRec = reinterpret_cast<int4 const *>(arena + d.offL) + d.bandSlot;
+        if (bv.ppw == 32 && !(tune & 1))
+        {
+            // one-thread-per-pair shapes: the whole trace of the pair is 16 bytes per row, two rows per sector; pull it
+            // into L2 now (last rows first), so that only the first window of the walk waits for HBM
+            uint4 const * tb = reinterpret_cast<uint4 const *>(bv.trace) + ((size_t)bv.slot << 1);
+            for (int s = (d.lb >> 1) - lane; s >= 0; s -= 32)
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(tb + (size_t)s * 64));
+        }
         int32_t sE = st.sEnd, vE = st.vEnd, hE = st.hEnd;
         int const dEnd = d.la - d.lb;
         if (dEnd > d.dHi || dEnd < d.dLo)
@@ -731,9 +746,39 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
     // ---- 3. subgradient marks, sequence part of the lower bound, matching candidates (:343-391) ----
     // 32 lines at a time: their interactions are numbered consecutively (prefix sum of the degrees) and dealt to
-    // the lanes, two per lane and round, so that the record loads of a round are all in flight together
+    // the lanes, kItems per lane and round, so that the record loads of a round are all in flight together.
+    constexpr int kItems = 4;
+    constexpr int kBitWords = 111;
     int32_t lbSeq = 0;
+    // sm.win is 256 words: [0, 33) offsets, then two bitmaps with one bit per interaction of the pair
     uint32_t * const sOff = sm.win;                                 // [33] first item of each of the 32 lines
+    uint32_t * const tieBits = sm.win + 34;                         // "is a tied top of its line"
+    uint32_t * const solBits = tieBits + kBitWords;                 // "... and its partner is in the solution"
+    // The cycle test of a tied top x of line l whose partner m is in the solution (:359-366) asks whether the reverse
+    // interaction is a tied top of m.  m is a line too, so this very loop answers that when it walks m's row: with
+    // the answers in a bitmap the test needs no record of m at all, and runs once all rows have been walked.  Pairs
+    // with more interactions than the bitmap holds read the two records instead (tie_direct).
+    bool const useBits = d.D <= 32 * kBitWords && !(tune & 8);
+    int const nBitWords = (d.D + 31) >> 5;
+    if (useBits)
+        for (int k = lane; k < 2 * kBitWords; k += 32) tieBits[k] = 0u;
+    auto tie_direct = [&](int x, bool inSol)
+    {
+        int4 const r1 = inter[2 * (size_t)x + 1];
+        int const rx = r1.x;
+        bool cycle = false;
+        if (inSol)
+        {
+            int4 const r0 = inter[2 * (size_t)x];
+            cycle = (r1.y + r0.z + inter[2 * (size_t)rx].w == edge[r0.x].y);
+        }
+        if (!cycle)
+        {
+            int const at = atomicAdd(&sm.misc[0], 2);
+            list[at] = x;                                           // subgradient +1
+            list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
+        }
+    };
     for (int base = 0; base < nLines; base += 32)
     {
         int const i = base + lane;
@@ -754,59 +799,75 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         sOff[lane] = (uint32_t)off;
         if (lane == 0) sOff[32] = (uint32_t)total;
         __syncwarp();
-        for (int t0 = 0; t0 < total; t0 += 64)
+        for (int t0 = 0; t0 < total; t0 += 32 * kItems)
         {
-            int4 r0[2];
-            int xs[2], es[2], is[2];
-            int32_t sqs[2], tops[2];
-            bool act[2];
+            int4 r0[kItems];
+            int xs[kItems], os[kItems];
             #pragma unroll
-            for (int u = 0; u < 2; ++u)
+            for (int u = 0; u < kItems; ++u)
             {
+                if (t0 + 32 * u >= total) break;                // uniform
                 int const t = t0 + 32 * u + lane;
-                act[u] = t < total;
                 int o = 0;                                      // owner: the last line that starts at or before item t
                 #pragma unroll
                 for (int step = 16; step > 0; step >>= 1)
                     if (sOff[o + step] <= (uint32_t)t) o += step;
-                es[u] = __shfl_sync(kFull, e, o);
-                sqs[u] = __shfl_sync(kFull, er.x, o);
-                tops[u] = __shfl_sync(kFull, er.y, o);
+                os[u] = o;
                 xs[u] = __shfl_sync(kFull, er.z, o) + (t - __shfl_sync(kFull, off, o));
-                is[u] = base + o;
                 r0[u] = make_int4(0, 0, 0, 0);
-                if (act[u]) r0[u] = inter[2 * (size_t)xs[u]];
+                if (t < total) r0[u] = inter[2 * (size_t)xs[u]];
             }
             #pragma unroll
-            for (int u = 0; u < 2; ++u)
+            for (int u = 0; u < kItems; ++u)
             {
-                if (!act[u]) continue;
-                int const x = xs[u], m = r0[u].x;
+                if (t0 + 32 * u >= total) break;                // uniform
+                int const o = os[u];
+                int const eo = __shfl_sync(kFull, e, o);
+                int32_t const sq = __shfl_sync(kFull, er.x, o), top = __shfl_sync(kFull, er.y, o);
+                if (t0 + 32 * u + lane >= total) continue;
+                int const m = r0[u].x;
                 uint32_t const pp = (uint32_t)r0[u].y;
                 int32_t const s = r0[u].z;
                 int const li = sm.lineOfA[pp >> 16];
                 bool const inSol = li >= 0 && (sm.linesRev[nLines - 1 - li] & 0xffffu) == (pp & 0xffffu);
-                if (sqs[u] + s + r0[u].w == tops[u])
+                if (sq + s + r0[u].w == top)
                 {
-                    int4 const r1 = inter[2 * (size_t)x + 1];
-                    int const rx = r1.x;
-                    bool cycle = false;
-                    if (inSol)
-                        cycle = (r1.y + s + inter[2 * (size_t)rx].w == edge[m].y);
-                    if (!cycle)
+                    if (useBits)
                     {
-                        int const at = atomicAdd(&sm.misc[0], 2);
-                        list[at] = x;                                   // subgradient +1
-                        list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
+                        atomicOr(&tieBits[xs[u] >> 5], 1u << (xs[u] & 31));
+                        if (inSol) atomicOr(&solBits[xs[u] >> 5], 1u << (xs[u] & 31));
                     }
+                    else
+                        tie_direct(xs[u], inSol);
                 }
-                if (inSol && es[u] < m)
+                if (inSol && eo < m)
                 {
                     int const at = atomicAdd(&sm.misc[1], 1);
                     unsigned long long const key = ((unsigned long long)(~((uint32_t)s ^ 0x80000000u)) << 32) |
-                                                   ((unsigned long long)is[u] << 16) | (unsigned long long)li;
+                                                   ((unsigned long long)(base + o) << 16) | (unsigned long long)li;
                     if (at < d.kCap) cand[at] = key; else sm.misc[11] = 2;
                 }
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    if (useBits)
+    {
+        for (int k = lane; k < nBitWords; k += 32)
+        {
+            uint32_t bits = tieBits[k];
+            uint32_t const sol = solBits[k];
+            while (bits)
+            {
+                int const j = __ffs((int)bits) - 1;
+                bits &= bits - 1u;
+                int const x = 32 * k + j;
+                int const rx = inter[2 * (size_t)x + 1].x;
+                if (((sol >> j) & 1u) && ((tieBits[rx >> 5] >> (rx & 31)) & 1u)) continue;     // cycle
+                int const at = atomicAdd(&sm.misc[0], 2);
+                list[at] = x;                                           // subgradient +1
+                list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
             }
         }
     }
@@ -927,13 +988,38 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         // ---- 8a. updateScores (:312-323): refresh the queue top of every touched edge -------------
         int32_t * __restrict__ vals = arena + (d.bandW > 0 ? d.offBVals : d.offVals);
         int32_t const * __restrict__ perm = arena + d.offPerm;
-        for (int i = lane; i < nList; i += 32)
+        // The list holds pairs (x, reverse of x): the multiplier of x went down (x was a tied top of its row, so the
+        // row's maximum has to be found again), the multiplier of the reverse entry went up (its row's maximum can
+        // only grow: max(top, new value), an atomic that commutes with the plain store of a full rescan of the row).
+        int const nPairs = nList >> 1;
+        if (tune & 2)
         {
-            size_t const di = (size_t)((uint32_t)list[i] & 0x7fffffffu);
+            // measurement switch: every entry rescans its row (the round-1d form)
+            for (int i = lane; i < nList; i += 32)
+            {
+                size_t const di = (size_t)((uint32_t)list[i] & 0x7fffffffu);
+                int const l = inter[2 * di + 1].z;
+                int4 const er = edge[l];
+                int32_t const sq = er.x;
+                int32_t top = sq;
+                for (int x = er.z; x < er.z + er.w; ++x)
+                {
+                    int4 const r0 = inter[2 * (size_t)x];
+                    top = max(top, sq + r0.z + r0.w);
+                }
+                reinterpret_cast<int32_t *>(edge + l)[1] = top;
+                vals[perm[l]] = top;
+            }
+            return;
+        }
+        for (int k = lane; k < nPairs; k += 32)
+        {
+            size_t const di = (size_t)((uint32_t)list[2 * k] & 0x7fffffffu);
             int const l = inter[2 * di + 1].z;              // owner of interaction di
             int4 const er = edge[l];
             int32_t const sq = er.x;
             int32_t top = sq;
+            #pragma unroll 4
             for (int x = er.z; x < er.z + er.w; ++x)
             {
                 int4 const r0 = inter[2 * (size_t)x];
@@ -941,6 +1027,15 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
             }
             reinterpret_cast<int32_t *>(edge + l)[1] = top;
             vals[perm[l]] = top;
+        }
+        for (int k = lane; k < nPairs; k += 32)
+        {
+            size_t const di = (size_t)((uint32_t)list[2 * k + 1] & 0x7fffffffu);
+            int4 const r0 = inter[2 * di];
+            int const l = inter[2 * di + 1].z;
+            int32_t const v = edge[l].x + r0.z + r0.w;
+            atomicMax(&reinterpret_cast<int32_t *>(edge + l)[1], v);
+            atomicMax(&vals[perm[l]], v);
         }
         return;
     }
@@ -1021,10 +1116,13 @@ cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state,
     // differ in length), and single-warp blocks let the SM refill per pair (measured: 4 % faster step than 4 warps)
     static int const warpsPerBlock = []() { char const * e = std::getenv("LARA_B200_POSTWARPS"); int v = e ? std::atoi(e) : 1;
                                             return v == 2 || v == 4 ? v : 1; }();
+    // measurement switches: bit 0 = no L2 prefetch of the trace, bit 1 = updateScores rescans every touched row,
+    // bit 2 = no prefetch of the row records, bit 3 = cycle test always from the two records (no tie bitmap)
+    static int const tune = []() { char const * e = std::getenv("LARA_B200_POSTTUNE"); return e ? std::atoi(e) : 0; }();
     size_t const smem = post_smem_per_warp(maxLa, maxLb, smemCand) * warpsPerBlock;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
     iterate_post_kernel<false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, outHdr, outLines,
-                                                                             outOff, activeCount, maxLa, maxLb, smemCand);
+                                                                             outOff, activeCount, maxLa, maxLb, smemCand, tune);
     return cudaGetLastError();
 }
 
@@ -1066,7 +1164,7 @@ cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * stat
     P.go = go; P.ge = ge;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
     iterate_post_kernel<true><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, nullptr, nullptr,
-                                                                            nullptr, nullptr, maxLa, maxLb, 0);
+                                                                            nullptr, nullptr, maxLa, maxLb, 0, 0);
     return cudaGetLastError();
 }
 

@@ -965,6 +965,16 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
             CK(cudaEventCreate(&dv.evRun0));
             CK(cudaEventCreate(&dv.evRun1));
             CK(post_configure_device());
+            // L2 fetch granularity (a hint; the driver default fetches 64 bytes per missed 32-byte sector): the post
+            // kernel reads isolated 32-byte records, the fill reads whole lines either way.  LARA_B200_L2FETCH = 32|64|128
+            if (char const * e = std::getenv("LARA_B200_L2FETCH"))
+            {
+                int const g = std::atoi(e);
+                if (g == 32 || g == 64 || g == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)g);
+                size_t got = 0;
+                cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
+                if (ctx->verbose) std::fprintf(stderr, "[lara_b200] dev %d L2 fetch granularity %zu\n", id, got);
+            }
             // keep freed blocks in the stream-ordered pool between batches
             cudaMemPool_t pool;
             CK(cudaDeviceGetDefaultMemPool(&pool, id));
