@@ -171,10 +171,22 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
             sub[4 * k] = x.x; sub[4 * k + 1] = x.y; sub[4 * k + 2] = x.z; sub[4 * k + 3] = x.w;
         }
     };
+    // Blocks of up to 8 diagonals are short: half a row of arithmetic does not cover an L2 hit, and such launches have
+    // too few warps to hide it (measured: the same 2,000 cycles per row as one thread per pair).  There the register
+    // pipeline is one row deeper: nxtA / nxtB hold the scores of the row after the one in subA / subB.
+    constexpr bool kDeep = Q <= 8;
     int32_t subA[Q], subB[Q];
+    int32_t nxtA[kDeep ? Q : 1], nxtB[kDeep ? Q : 1];
     #pragma unroll
     for (int j = 0; j < Q; ++j) { subA[j] = kDpNeg; subB[j] = kDpNeg; }
     if (1 - g >= 1 && 1 - g <= lb) load_run(subA, 1 - g, 2 * g);
+    if constexpr (kDeep)
+    {
+        #pragma unroll
+        for (int j = 0; j < Q; ++j) { nxtA[j] = kDpNeg; nxtB[j] = kDpNeg; }
+        if (1 - g >= 1 && 1 - g <= lb) load_run(subB, 1 - g, 2 * g + 1);
+        if (2 - g >= 1 && 2 - g <= lb) load_run(nxtA, 2 - g, 2 * g);
+    }
 
     int const nIter = lbMax + G;
     uint32_t twA[2] = {0u, 0u};                                     // G == 1: block A's unit waits for block B's
@@ -182,7 +194,8 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
     {
         int const r = i - g + 1;
         bool const rowValid = r >= 1 && r <= lb;
-        if (rowValid) load_run(subB, r, 2 * g + 1);
+        if constexpr (kDeep) { if (r + 1 >= 1 && r + 1 <= lb) load_run(nxtB, r + 1, 2 * g + 1); }
+        else if (rowValid) load_run(subB, r, 2 * g + 1);
         // the register pipeline is half a row deep; under load HBM answers later than that, so the rows
         // kPrefetchRows ahead are pulled into L2 meanwhile (a warp's 16-byte chunks of one row are contiguous)
         if (r + kPrefetchRows <= lb && r + kPrefetchRows >= 1)
@@ -225,7 +238,13 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
                 else store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g)) * PPW + gs, tw);
             }
         }
-        if (r + 1 >= 1 && r + 1 <= lb) load_run(subA, r + 1, 2 * g);
+        if constexpr (kDeep)
+        {
+            #pragma unroll
+            for (int j = 0; j < Q; ++j) subA[j] = nxtA[j];
+            if (r + 2 >= 1 && r + 2 <= lb) load_run(nxtA, r + 2, 2 * g);
+        }
+        else if (r + 1 >= 1 && r + 1 <= lb) load_run(subA, r + 1, 2 * g);
         // ------------------------------ block B ----------------------------------------------------------------
         {
             int32_t sU = __shfl_down_sync(kFull, SA[0], 1, G);
@@ -264,6 +283,11 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
                 }
                 else store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g + 1)) * PPW + gs, tw);
             }
+        }
+        if constexpr (kDeep)
+        {
+            #pragma unroll
+            for (int j = 0; j < Q; ++j) subB[j] = nxtB[j];
         }
     }
     if (bEnd >= 0 && (bEnd >> 1) == g)
