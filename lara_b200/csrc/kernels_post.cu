@@ -82,7 +82,8 @@ struct WarpSmem
 {
     int16_t * lineOfA;      // [maxLa]  line index of A position or -1
     uint32_t * linesRev;    // [maxLb]  (a << 16) | b in traceback order (last line first)
-    int32_t * curE;         // [maxLb]  compact edge id per line (alignment order)
+    int32_t * curE;         // [maxLb]  compact edge id of the k-th line that has interactions (alignment order)
+    int16_t * workLine;     // [maxLb]  ... and its line index
     uint8_t * matched;      // [maxLb]
     unsigned long long * cand;  // [smemCand]
     int32_t * misc;         // [32]: 0 nList, 1 nCand, 2 matchScore, 3..10 selection weights, 11 error, 16..23 selection
@@ -611,14 +612,17 @@ __device__ int32_t greedy_matching(unsigned long long const * keys, int K, int l
     return warp_sum(score);
 }
 
-__device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b)
+__device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b, bool & hasInter)
 {
+    hasInter = true;                            // without a row record: unknown, the edge record tells
     if (d.offRowRec)
     {
-        // narrow band: the row's active cells fit one word, stored next to the id of the row's first edge
-        int2 const rec = __ldg(reinterpret_cast<int2 const *>(arena + d.offRowRec) + a);
+        // narrow band: the row's active cells fit one word, stored next to the id of the row's first edge and the
+        // word of the cells that have interactions
+        int4 const rec = __ldg(reinterpret_cast<int4 const *>(arena + d.offRowRec) + a);
         int const k = b - (a - d.dHi);
         if (k < 0 || k > 31 || !(((uint32_t)rec.y >> k) & 1u)) return -1;
+        hasInter = ((uint32_t)rec.z >> k) & 1u;
         return rec.x + __popc((uint32_t)rec.y & ((1u << k) - 1u));
     }
     uint32_t const * bits = (uint32_t const *)(arena + d.offBits) + (size_t)a * d.bitWords;
@@ -631,6 +635,11 @@ __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __res
     if (!((word >> (b & 31)) & 1u)) return -1;
     return e + __popc(word & ((1u << (b & 31)) - 1u));
 }
+__device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b)
+{
+    bool h;
+    return edge_of(d, arena, a, b, h);
+}
 
 // 80 registers (6 x 128 threads): with one-warp blocks 24 pairs per SM.  More pairs per SM (72 or 64 registers, or
 // more shared memory at the cost of L1) measured slower, fewer (90 registers, what ptxas takes unbounded) too.
@@ -639,7 +648,7 @@ __global__ void __launch_bounds__(128, 6)
 iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
                     int32_t * __restrict__ arena, DevParams P, PairOutHdr * __restrict__ outHdr,
                     int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
-                    int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand, int tune)
+                    int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand, int tune, DevInputs in)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     int const warpInBlock = threadIdx.x >> 5;
@@ -655,7 +664,8 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     // carve the per-warp shared memory
     size_t const candBytes = (size_t)smemCand * 8;
     size_t const lb4 = ((size_t)maxLb * 4 + 15) / 16 * 16;
-    size_t const perWarp = candBytes + 128 + 1024 + 2 * lb4 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    size_t const perWarp = candBytes + 128 + 1024 + 2 * lb4 + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb * 2 + 15) / 16 * 16 +
+                           ((size_t)maxLb + 15) / 16 * 16;
     unsigned char * base = smemRaw + (size_t)warpInBlock * perWarp;
     WarpSmem sm;
     sm.cand = (unsigned long long *)base;                     base += candBytes;
@@ -664,15 +674,16 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     sm.linesRev = (uint32_t *)base;                           base += lb4;
     sm.curE = (int32_t *)base;                                base += lb4;
     sm.lineOfA = (int16_t *)base;                             base += ((size_t)maxLa * 2 + 15) / 16 * 16;
+    sm.workLine = (int16_t *)base;                            base += ((size_t)maxLb * 2 + 15) / 16 * 16;
     sm.matched = (uint8_t *)base;
 
     int const la = d.la, lb = d.lb;
     (void)lb;
     if (d.offRowRec && !(tune & 4))
     {
-        // the row records of the edge lookup (step 2; 8 bytes per row): into L2 while the traceback runs
-        int2 const * rr = reinterpret_cast<int2 const *>(arena + d.offRowRec);
-        for (int a = 4 * lane; a < la; a += 128)
+        // the row records of the edge lookup (step 2; 16 bytes per row): into L2 while the traceback runs
+        int4 const * rr = reinterpret_cast<int4 const *>(arena + d.offRowRec);
+        for (int a = 2 * lane; a < la; a += 64)
             asm volatile("prefetch.global.L2 [%0];" :: "l"(rr + a));
     }
 
@@ -732,15 +743,40 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     unsigned long long * cand = candInSmem ? sm.cand : (unsigned long long *)(arena + d.offCand);
 
     // ---- 2. lines -> edge ids --------------------------------------------------------------------
-    for (int i = lane; i < nLines; i += 32)
+    // A line whose edge has no interaction only adds its sequence score to the lower bound (:343-349), a function
+    // of the two bases (setup_count_kernel); the lines that have interactions are gathered, in alignment order, for
+    // step 3, which then reads the edge records of those lines only.
+    int32_t lbSeq = 0;
+    int nWork = 0;
     {
-        uint32_t const ab = sm.linesRev[nLines - 1 - i];
-        int const a = (int)(ab >> 16), b = (int)(ab & 0xffffu);
-        sm.lineOfA[a] = (int16_t)i;
-        int const e = edge_of(d, arena, a, b);
-        if (e < 0) sm.misc[11] = 1;            // "Alignment match where no alignment edge is defined!"
-        sm.curE[i] = e;
-        sm.matched[i] = 0;
+        uint8_t const * __restrict__ seqA = in.seqCat + in.seqOff[d.seqFirst];
+        uint8_t const * __restrict__ seqB = in.seqCat + in.seqOff[d.seqSecond];
+        float const scale = st.scale;
+        for (int i0 = 0; i0 < nLines; i0 += 32)
+        {
+            int const i = i0 + lane;
+            bool work = false;
+            int e = -1;
+            if (i < nLines)
+            {
+                uint32_t const ab = sm.linesRev[nLines - 1 - i];
+                int const a = (int)(ab >> 16), b = (int)(ab & 0xffffu);
+                sm.lineOfA[a] = (int16_t)i;
+                e = edge_of(d, arena, a, b, work);
+                if (e < 0) { sm.misc[11] = 1; work = false; }   // "Alignment match where no alignment edge is defined!"
+                else if (!work)
+                    lbSeq += __float2int_rz(__fmul_rn(scale, __int2float_rn(P.tab[(int)seqA[a] * 5 + (int)seqB[b]])));
+                sm.matched[i] = 0;
+            }
+            unsigned const bal = __ballot_sync(kFull, work);
+            if (work)
+            {
+                int const k = nWork + __popc(bal & ((1u << lane) - 1u));
+                sm.curE[k] = e;
+                sm.workLine[k] = (int16_t)i;
+            }
+            nWork += __popc(bal);
+        }
     }
     __syncwarp();
 
@@ -749,7 +785,6 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     // the lanes, kItems per lane and round, so that the record loads of a round are all in flight together.
     constexpr int kItems = 4;
     constexpr int kBitWords = 111;
-    int32_t lbSeq = 0;
     // sm.win is 256 words: [0, 33) offsets, then two bitmaps with one bit per interaction of the pair
     uint32_t * const sOff = sm.win;                                 // [33] first item of each of the 32 lines
     uint32_t * const tieBits = sm.win + 34;                         // "is a tied top of its line"
@@ -779,10 +814,9 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
             list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
         }
     };
-    for (int base = 0; base < nLines; base += 32)
+    for (int base = 0; base < nWork; base += 32)
     {
-        int const i = base + lane;
-        int const e = i < nLines ? sm.curE[i] : -1;
+        int const e = base + lane < nWork ? sm.curE[base + lane] : -1;
         int4 er = make_int4(0, 0, 0, 0);
         if (e >= 0) er = edge[e];
         lbSeq += er.x;
@@ -844,7 +878,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
                 {
                     int const at = atomicAdd(&sm.misc[1], 1);
                     unsigned long long const key = ((unsigned long long)(~((uint32_t)s ^ 0x80000000u)) << 32) |
-                                                   ((unsigned long long)(base + o) << 16) | (unsigned long long)li;
+                                                   ((unsigned long long)(uint16_t)sm.workLine[base + o] << 16) | (unsigned long long)li;
                     if (at < d.kCap) cand[at] = key; else sm.misc[11] = 2;
                 }
             }
@@ -897,10 +931,10 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     {
         // every top is part of a cycle (:397-409): add the structure score of the first tied top
         int32_t add = 0;
-        for (int i = lane; i < nLines; i += 32)
+        for (int k = lane; k < nWork; k += 32)
         {
-            int const e = sm.curE[i];
-            if (e < 0) continue;
+            int const e = sm.curE[k];
+            int const i = sm.workLine[k];
             int4 const er = edge[e];
             int32_t const sq = er.x, top = er.y;
             int found = -1;
@@ -1089,7 +1123,8 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
 
 size_t post_smem_per_warp(int maxLa, int maxLb, int smemCand)
 {
-    return (size_t)smemCand * 8 + 128 + 1024 + 2 * (((size_t)maxLb * 4 + 15) / 16 * 16) + ((size_t)maxLa * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
+    return (size_t)smemCand * 8 + 128 + 1024 + 2 * (((size_t)maxLb * 4 + 15) / 16 * 16) + ((size_t)maxLa * 2 + 15) / 16 * 16 +
+           ((size_t)maxLb * 2 + 15) / 16 * 16 + ((size_t)maxLb + 15) / 16 * 16;
 }
 
 } // namespace
@@ -1109,7 +1144,8 @@ cudaError_t post_configure_device()
 
 cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                 DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
-                                int32_t * activeCount, int maxLa, int maxLb, int smemCand, cudaStream_t stream)
+                                int32_t * activeCount, int maxLa, int maxLb, int smemCand, DevInputs const & in,
+                                cudaStream_t stream)
 {
     if (n <= 0) return cudaSuccess;
     // one warp (= one pair) per block: pairs differ a lot in run time (finished pairs return at once, alignments
@@ -1122,7 +1158,7 @@ cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state,
     size_t const smem = post_smem_per_warp(maxLa, maxLb, smemCand) * warpsPerBlock;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
     iterate_post_kernel<false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, outHdr, outLines,
-                                                                             outOff, activeCount, maxLa, maxLb, smemCand, tune);
+                                                                             outOff, activeCount, maxLa, maxLb, smemCand, tune, in);
     return cudaGetLastError();
 }
 
@@ -1164,7 +1200,7 @@ cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * stat
     P.go = go; P.ge = ge;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
     iterate_post_kernel<true><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, nullptr, nullptr,
-                                                                            nullptr, nullptr, maxLa, maxLb, 0, 0);
+                                                                            nullptr, nullptr, maxLa, maxLb, 0, 0, DevInputs{});
     return cudaGetLastError();
 }
 

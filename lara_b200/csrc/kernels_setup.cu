@@ -277,7 +277,8 @@ setup_count_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__
                 uint32_t word = 0u;
                 if (lo >= 0) word = strip_bits(bits + (size_t)a * bitWords, bitWords, lo, 32);
                 else if (lo > -32) word = strip_bits(bits + (size_t)a * bitWords, bitWords, 0, 32) << (-lo);
-                reinterpret_cast<int2 *>(arena + d.offRowRec)[a] = make_int2(carry + ex, (int)word);
+                // third word: the cells that have interactions, set by setup_fill_kernel
+                reinterpret_cast<int4 *>(arena + d.offRowRec)[a] = make_int4(carry + ex, (int)word, 0, 0);
             }
         }
         carry += total;
@@ -456,6 +457,11 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
         {
             int const x0 = ioff[e], x1 = ioff[e + 1];
             edge[e] = make_int4(seqScore[e], pv[e], x0, x1 - x0);
+            if (d.offRowRec && x1 > x0)
+            {
+                int const ab = cell[e], a = ab >> 16, b = ab & 0xffff;
+                atomicOr(&reinterpret_cast<int32_t *>(arena + d.offRowRec)[4 * a + 2], (int)(1u << (b - (a - d.dHi))));
+            }
             for (int x = x0; x < x1; ++x)
             {
                 int const m = part[x];

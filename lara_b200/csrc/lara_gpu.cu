@@ -115,6 +115,7 @@ struct lara_ctx
     int bandMinWarps = 400;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
     bool band24 = true;                     // 24-diagonal one-thread-per-pair shape (env LARA_B200_BAND24=0: off)
     int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
+    bool fillPrio = false;                  // DP launches on high-priority streams (env LARA_B200_FILLPRIO)
     int verbose = 0;                        // env LARA_B200_VERBOSE=1: host-side stage times of every batch on stderr
     bool compactSlots = false;              // repack the DP slot lists as pairs finish (env LARA_B200_COMPACT=1); measured:
                                             // the DP is HBM-bound, idle lanes cost nothing, repacking costs locality
@@ -473,7 +474,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     {
         PairDesc & d = desc[(size_t)i];
         sizeB += 8 * align4(std::max(d.E, 1)) + align4(d.E + 1);
-        if (d.bandW > 0 && d.bandW <= 32) sizeB += align4(2ll * d.la);
+        if (d.bandW > 0 && d.bandW <= 32) sizeB += align4(4ll * d.la);
         if (d.bandW == 0)
         {
             if (d.R > kMaxR)
@@ -497,7 +498,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         d.offCell = rB.take(d.E); d.offSeqScore = rB.take(d.E); d.offPv = rB.take(d.E); d.offPerm = rB.take(d.E);
         d.offIoff = rB.take(d.E + 1);
         d.offEdge = rB.take(4ll * d.E);
-        if (d.bandW > 0 && d.bandW <= 32) d.offRowRec = rB.take(2ll * d.la);
+        if (d.bandW > 0 && d.bandW <= 32) d.offRowRec = rB.take(4ll * d.la);
         if (d.bandW > 0)
         {
             if (!pilot)
@@ -605,10 +606,15 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
                 std::fprintf(stderr, "[lara_b200]   DP class full matrix R=%d: %d pairs\n", std::get<0>(c), std::get<2>(c));
         }
     if (!wk.evFork) CK(cudaEventCreateWithFlags(&wk.evFork, cudaEventDisableTiming));
-    while (wk.aux.size() + 1 < cls.size())
+    // fillPrio: every DP launch runs on a high-priority side stream, so that its few, long-running blocks are placed as
+    // soon as blocks of the other worker's post kernel retire instead of queueing behind all of them
+    size_t const auxBase = ctx.fillPrio ? 0 : 1;                  // class k runs on aux[k - auxBase] (k < auxBase: on s)
+    while (wk.aux.size() + auxBase < cls.size())
     {
         cudaStream_t st; cudaEvent_t ev;
-        CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        int prLo = 0, prHi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&prLo, &prHi));
+        CK(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, ctx.fillPrio ? prHi : prLo));
         CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         wk.aux.push_back(st); wk.auxJoin.push_back(ev);
     }
@@ -644,12 +650,12 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     {
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it], s));
         // the largest class on the worker's stream, the others beside it on side streams (fork / join by events)
-        if (cls.size() > 1) CK(cudaEventRecord(wk.evFork, s));
+        if (cls.size() > auxBase) CK(cudaEventRecord(wk.evFork, s));
         for (size_t k = 0; k < cls.size(); ++k)
         {
             auto const & c = cls[k];
-            cudaStream_t const sk = k == 0 ? s : wk.aux[k - 1];
-            if (k > 0) CK(cudaStreamWaitEvent(sk, wk.evFork, 0));
+            cudaStream_t const sk = k < auxBase ? s : wk.aux[k - auxBase];
+            if (k >= auxBase) CK(cudaStreamWaitEvent(sk, wk.evFork, 0));
             int32_t const * const lst = dIdx + (size_t)clsSide[k] * idxStride + std::get<1>(c);
             if (clsCount[k] == 0) continue;
             if (std::get<3>(c) >= 0)
@@ -657,13 +663,13 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
                                      lst, dDesc, dState, arena, dp.go, dp.ge, sk));
             else
                 CK(launch_gotoh_fill(std::get<0>(c), clsCount[k], lst, dDesc, dState, arena, dv.negBuf, dp.go, dp.ge, sk));
-            if (k > 0) CK(cudaEventRecord(wk.auxJoin[k - 1], sk));
+            if (k >= auxBase) CK(cudaEventRecord(wk.auxJoin[k - auxBase], sk));
             wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
         }
-        for (size_t k = 1; k < cls.size(); ++k) CK(cudaStreamWaitEvent(s, wk.auxJoin[k - 1], 0));
+        for (size_t k = auxBase; k < cls.size(); ++k) CK(cudaStreamWaitEvent(s, wk.auxJoin[k - auxBase], 0));
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 1], s));
         CK(launch_iterate_post(n, dDesc, dState, arena, dp, dv.dOutHdr + begin, dv.dOutLines, dv.dOutOff + begin,
-                               wk.dActive, maxLa, maxLb, smemCand, s));
+                               wk.dActive, maxLa, maxLb, smemCand, dv.in, s));
         wk.stats.kernel_launches += 1;
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 2], s));
         itersRun = it + 1;
@@ -919,6 +925,7 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_BAND24")) ctx->band24 = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_BANDQ")) ctx->bandForceQ = std::atoi(e);
     if (char const * e = std::getenv("LARA_B200_VERBOSE")) ctx->verbose = std::atoi(e);
+    if (char const * e = std::getenv("LARA_B200_FILLPRIO")) ctx->fillPrio = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_COMPACT")) ctx->compactSlots = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_SMEMCAND")) ctx->postSmemCand = std::max(32, std::min(2048, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));

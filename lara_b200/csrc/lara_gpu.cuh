@@ -80,7 +80,7 @@ struct PairDesc
     int64_t offEdge;            // per edge, 16 bytes: { seqScore, pv (queue top == pssm value), ioff, degree }   [E]
     int64_t offInter;           // per interaction, 32 bytes: { partner edge, partner cell, structScore, dual,
                                 //                               reverse index, seqScore of the partner, owner edge, 0 }  [D]
-    int64_t offRowRec;          // bands of <= 32 diagonals, per row a of the bitmap, 8 bytes: { id of the row's first edge,
+    int64_t offRowRec;          // bands of <= 32 diagonals, per row a of the bitmap, 16 bytes: { id of the row's first edge,
                                 //   activity bits of b = a - dHi .. a - dHi + 31 }   [la]   (0: not present)
     int64_t offLines;           // current lines  (a << 16) | b  [lb]
     int64_t offBest;            // best lines     (a << 16) | b | matched << 31  [lb]
@@ -170,7 +170,8 @@ __host__ __device__ inline int64_t band_val_index(int bandW, int ppw, int slot, 
 // traceback + valid_solution + matching + bounds + update for all n pairs of the batch
 cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                 DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
-                                int32_t * activeCount, int maxLa, int maxLb, int smemCand, cudaStream_t stream);
+                                int32_t * activeCount, int maxLa, int maxLb, int smemCand, DevInputs const & in,
+                                cudaStream_t stream);
 // traceback only (unit entry point lara_gpu_gotoh_batch)
 cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                   int32_t go, int32_t ge, int maxLa, int maxLb, cudaStream_t stream);
