@@ -732,8 +732,8 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         return;
     }
 
-    // per edge { seqScore, pv, ioff, degree }, per interaction { partner, partner cell, structScore, dual } and
-    // { reverse index, seqScore of the partner, owner, 0 }  (lara_gpu.cuh: offEdge, offInter)
+    // per edge { seqScore, pv, ioff, degree }, per interaction { reverse index, partner cell, structScore, dual } and
+    // { partner edge, seqScore of the partner, owner, 0 }  (lara_gpu.cuh: offEdge, offInter)
     int4 * __restrict__ edge = reinterpret_cast<int4 *>(arena + d.offEdge);
     int4 * __restrict__ inter = reinterpret_cast<int4 *>(arena + d.offInter);
     int32_t * __restrict__ list = arena + d.offList;
@@ -788,35 +788,36 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     // sm.win is 256 words: [0, 33) offsets, then two bitmaps with one bit per interaction of the pair
     uint32_t * const sOff = sm.win;                                 // [33] first item of each of the 32 lines
     uint32_t * const tieBits = sm.win + 34;                         // "is a tied top of its line"
-    uint32_t * const solBits = tieBits + kBitWords;                 // "... and its partner is in the solution"
+    uint32_t * const metBits = tieBits + kBitWords;                 // "one of x and its reverse has been seen" (bit min(x, rev))
     // The cycle test of a tied top x of line l whose partner m is in the solution (:359-366) asks whether the reverse
-    // interaction is a tied top of m.  m is a line too, so this very loop answers that when it walks m's row: with
-    // the answers in a bitmap the test needs no record of m at all, and runs once all rows have been walked.  Pairs
-    // with more interactions than the bitmap holds read the two records instead (tie_direct).
+    // interaction is a tied top of m.  m is a line too, so this very loop also walks m's row.  Whichever of x and its
+    // reverse is seen second (an atomic on the pair's bit decides) finds the other one's answer in the bitmap and
+    // settles both: no record of m is read.  Pairs with more interactions than the bitmaps hold read the two records
+    // instead (tie_direct).
     bool const useBits = d.D <= 32 * kBitWords && !(tune & 8);
-    int const nBitWords = (d.D + 31) >> 5;
     if (useBits)
         for (int k = lane; k < 2 * kBitWords; k += 32) tieBits[k] = 0u;
-    auto tie_direct = [&](int x, bool inSol)
+    auto mark = [&](int x, int rx)
     {
-        int4 const r1 = inter[2 * (size_t)x + 1];
-        int const rx = r1.x;
+        int const at = atomicAdd(&sm.misc[0], 2);
+        list[at] = x;                                           // subgradient +1
+        list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
+    };
+    auto tie_direct = [&](int x, int rx, int32_t s, bool inSol)
+    {
         bool cycle = false;
         if (inSol)
         {
-            int4 const r0 = inter[2 * (size_t)x];
-            cycle = (r1.y + r0.z + inter[2 * (size_t)rx].w == edge[r0.x].y);
+            int4 const r1 = inter[2 * (size_t)x + 1];           // { partner edge, its seqScore, owner, 0 }
+            cycle = (r1.y + s + inter[2 * (size_t)rx].w == edge[r1.x].y);
         }
-        if (!cycle)
-        {
-            int const at = atomicAdd(&sm.misc[0], 2);
-            list[at] = x;                                           // subgradient +1
-            list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
-        }
+        if (!cycle) mark(x, rx);
     };
     for (int base = 0; base < nWork; base += 32)
     {
         int const e = base + lane < nWork ? sm.curE[base + lane] : -1;
+        int const myLine = e >= 0 ? sm.workLine[base + lane] : 0;
+        uint32_t const myCell = e >= 0 ? sm.linesRev[nLines - 1 - myLine] : 0u;
         int4 er = make_int4(0, 0, 0, 0);
         if (e >= 0) er = edge[e];
         lbSeq += er.x;
@@ -849,60 +850,57 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
                 os[u] = o;
                 xs[u] = __shfl_sync(kFull, er.z, o) + (t - __shfl_sync(kFull, off, o));
                 r0[u] = make_int4(0, 0, 0, 0);
-                if (t < total) r0[u] = inter[2 * (size_t)xs[u]];
+                if (t < total) r0[u] = inter[2 * (size_t)xs[u]];    // { reverse interaction, partner cell, structScore, dual }
             }
             #pragma unroll
             for (int u = 0; u < kItems; ++u)
             {
                 if (t0 + 32 * u >= total) break;                // uniform
                 int const o = os[u];
-                int const eo = __shfl_sync(kFull, e, o);
+                uint32_t const cellO = __shfl_sync(kFull, myCell, o);
+                int const lineO = __shfl_sync(kFull, myLine, o);
                 int32_t const sq = __shfl_sync(kFull, er.x, o), top = __shfl_sync(kFull, er.y, o);
-                if (t0 + 32 * u + lane >= total) continue;
-                int const m = r0[u].x;
+                bool const valid = t0 + 32 * u + lane < total;
+                int const x = xs[u], rx = r0[u].x;
                 uint32_t const pp = (uint32_t)r0[u].y;
                 int32_t const s = r0[u].z;
-                int const li = sm.lineOfA[pp >> 16];
-                bool const inSol = li >= 0 && (sm.linesRev[nLines - 1 - li] & 0xffffu) == (pp & 0xffffu);
-                if (sq + s + r0[u].w == top)
+                int li = -1;
+                bool inSol = false, tied = false;
+                if (valid)
                 {
-                    if (useBits)
-                    {
-                        atomicOr(&tieBits[xs[u] >> 5], 1u << (xs[u] & 31));
-                        if (inSol) atomicOr(&solBits[xs[u] >> 5], 1u << (xs[u] & 31));
-                    }
-                    else
-                        tie_direct(xs[u], inSol);
+                    li = sm.lineOfA[pp >> 16];
+                    inSol = li >= 0 && (sm.linesRev[nLines - 1 - li] & 0xffffu) == (pp & 0xffffu);
+                    tied = sq + s + r0[u].w == top;
                 }
-                if (inSol && eo < m)
+                if (useBits)
+                {
+                    // every tied bit of this round is set before any lane asks for one
+                    if (tied && inSol) atomicOr(&tieBits[x >> 5], 1u << (x & 31));
+                    __syncwarp();
+                    if (inSol)
+                    {
+                        int const lo = min(x, rx);
+                        uint32_t const old = atomicOr(&metBits[lo >> 5], 1u << (lo & 31));
+                        if ((old >> (lo & 31)) & 1u)
+                        {
+                            bool const tiedR = (tieBits[rx >> 5] >> (rx & 31)) & 1u;
+                            if (tied && !tiedR) mark(x, rx);
+                            else if (tiedR && !tied) mark(rx, x);
+                        }
+                    }
+                    else if (tied) mark(x, rx);
+                }
+                else if (tied) tie_direct(x, rx, s, inSol);
+                // ids ascend in cell order: "line < partner" (:372) is a comparison of the two cells
+                if (inSol && cellO < pp)
                 {
                     int const at = atomicAdd(&sm.misc[1], 1);
                     unsigned long long const key = ((unsigned long long)(~((uint32_t)s ^ 0x80000000u)) << 32) |
-                                                   ((unsigned long long)(uint16_t)sm.workLine[base + o] << 16) | (unsigned long long)li;
+                                                   ((unsigned long long)(uint32_t)lineO << 16) | (unsigned long long)li;
                     if (at < d.kCap) cand[at] = key; else sm.misc[11] = 2;
                 }
             }
             __syncwarp();
-        }
-    }
-    __syncwarp();
-    if (useBits)
-    {
-        for (int k = lane; k < nBitWords; k += 32)
-        {
-            uint32_t bits = tieBits[k];
-            uint32_t const sol = solBits[k];
-            while (bits)
-            {
-                int const j = __ffs((int)bits) - 1;
-                bits &= bits - 1u;
-                int const x = 32 * k + j;
-                int const rx = inter[2 * (size_t)x + 1].x;
-                if (((sol >> j) & 1u) && ((tieBits[rx >> 5] >> (rx & 31)) & 1u)) continue;     // cycle
-                int const at = atomicAdd(&sm.misc[0], 2);
-                list[at] = x;                                           // subgradient +1
-                list[at + 1] = (int32_t)((uint32_t)rx | 0x80000000u);   // subgradient -1
-            }
         }
     }
     lbSeq = warp_sum(lbSeq);
@@ -935,6 +933,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
         {
             int const e = sm.curE[k];
             int const i = sm.workLine[k];
+            uint32_t const myCell = sm.linesRev[nLines - 1 - i];
             int4 const er = edge[e];
             int32_t const sq = er.x, top = er.y;
             int found = -1;
@@ -943,7 +942,7 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
             for (int x = er.z; x < er.z + er.w && found < 0 && !selfFirst; ++x)
             {
                 int4 const r0 = inter[2 * (size_t)x];
-                if (r0.x > e && sq == top) { selfFirst = true; break; }
+                if ((uint32_t)r0.y > myCell && sq == top) { selfFirst = true; break; }
                 if (sq + r0.z + r0.w == top) { found = x; rf = r0; }
             }
             if (found >= 0 && !selfFirst)

@@ -465,8 +465,8 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
             for (int x = x0; x < x1; ++x)
             {
                 int const m = part[x];
-                inter[2 * (size_t)x] = make_int4(m, ppos[x], sc[x], 0);
-                inter[2 * (size_t)x + 1] = make_int4(rev[x], seqScore[m], e, 0);
+                inter[2 * (size_t)x] = make_int4(rev[x], ppos[x], sc[x], 0);
+                inter[2 * (size_t)x + 1] = make_int4(m, seqScore[m], e, 0);
             }
         }
     }

@@ -78,10 +78,10 @@ struct PairDesc
     // records read by the iteration kernel (written at the end of the set-up from the arrays above, which stay
     // as the build-time form; pv and dual live only here afterwards):
     int64_t offEdge;            // per edge, 16 bytes: { seqScore, pv (queue top == pssm value), ioff, degree }   [E]
-    int64_t offInter;           // per interaction, 32 bytes: { partner edge, partner cell, structScore, dual,
-                                //                               reverse index, seqScore of the partner, owner edge, 0 }  [D]
+    int64_t offInter;           // per interaction, 32 bytes: { reverse index, partner cell, structScore, dual,
+                                //                               partner edge, seqScore of the partner, owner edge, 0 }  [D]
     int64_t offRowRec;          // bands of <= 32 diagonals, per row a of the bitmap, 16 bytes: { id of the row's first edge,
-                                //   activity bits of b = a - dHi .. a - dHi + 31 }   [la]   (0: not present)
+                                //   activity bits of b = a - dHi .. a - dHi + 31, of those the cells with interactions, 0 }   [la]   (0: not present)
     int64_t offLines;           // current lines  (a << 16) | b  [lb]
     int64_t offBest;            // best lines     (a << 16) | b | matched << 31  [lb]
     int64_t offCand;            // global candidate buffer for the matching sort, 2 words each [2 * kCap] (8-byte aligned)
