@@ -644,18 +644,15 @@ __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __res
 // 80 registers (6 x 128 threads): with one-warp blocks 24 pairs per SM.  More pairs per SM (72 or 64 registers, or
 // more shared memory at the cost of L1) measured slower, fewer (90 registers, what ptxas takes unbounded) too.
 template <bool kTracebackOnly>
-__global__ void __launch_bounds__(128, 6)
-iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
-                    int32_t * __restrict__ arena, DevParams P, PairOutHdr * __restrict__ outHdr,
-                    int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
-                    int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand, int tune, DevInputs in)
+__device__ __forceinline__ void
+iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
+                  int32_t * __restrict__ arena, DevParams const & P, PairOutHdr * __restrict__ outHdr,
+                  int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
+                  int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand, int tune, DevInputs const & in)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     int const warpInBlock = threadIdx.x >> 5;
     int const lane = threadIdx.x & 31;
-    int const p = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
-    if (p >= n)
-        return;
     PairState & st = state[p];
     if (st.done)
         return;
@@ -1120,6 +1117,37 @@ iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __res
     }
 }
 
+// Two launch forms.  workCounter == nullptr: warp w of the grid takes pair w.  Otherwise the grid is a fixed number of
+// one-warp blocks per SM (all of them resident from the start, so that a DP launch of another worker queued behind this
+// one is placed at once instead of waiting for the last wave of this grid) and every warp pulls pairs from the counter.
+template <bool kTracebackOnly, bool kPersistent>
+__global__ void __launch_bounds__(kPersistent ? 32 : 128, kPersistent ? 20 : 6)
+iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
+                    int32_t * __restrict__ arena, DevParams P, PairOutHdr * __restrict__ outHdr,
+                    int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
+                    int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand, int tune, DevInputs in,
+                    int32_t * __restrict__ workCounter)
+{
+    if (!kPersistent)
+    {
+        int const p = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
+        if (p < n)
+            iterate_post_pair<kTracebackOnly>(p, desc, state, arena, P, outHdr, outLines, outOff, activeCount, maxLa, maxLb,
+                                              smemCand, tune, in);
+        return;
+    }
+    for (;;)
+    {
+        __syncwarp();
+        int p = 0;
+        if ((threadIdx.x & 31) == 0) p = atomicAdd(workCounter, 1);
+        p = __shfl_sync(kFull, p, 0);
+        if (p >= n) break;
+        iterate_post_pair<kTracebackOnly>(p, desc, state, arena, P, outHdr, outLines, outOff, activeCount, maxLa, maxLb,
+                                          smemCand, tune, in);
+    }
+}
+
 size_t post_smem_per_warp(int maxLa, int maxLb, int smemCand)
 {
     return (size_t)smemCand * 8 + 128 + 1024 + 2 * (((size_t)maxLb * 4 + 15) / 16 * 16) + ((size_t)maxLa * 2 + 15) / 16 * 16 +
@@ -1136,15 +1164,17 @@ cudaError_t post_configure_device()
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&maxOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(iterate_post_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
+    e = cudaFuncSetAttribute(iterate_post_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(iterate_post_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
+    e = cudaFuncSetAttribute(iterate_post_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(iterate_post_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
 }
 
 cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                 DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
                                 int32_t * activeCount, int maxLa, int maxLb, int smemCand, DevInputs const & in,
-                                cudaStream_t stream)
+                                cudaStream_t stream, int32_t * workCounter, int gridWarps)
 {
     if (n <= 0) return cudaSuccess;
     // one warp (= one pair) per block: pairs differ a lot in run time (finished pairs return at once, alignments
@@ -1156,8 +1186,12 @@ cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state,
     static int const tune = []() { char const * e = std::getenv("LARA_B200_POSTTUNE"); return e ? std::atoi(e) : 0; }();
     size_t const smem = post_smem_per_warp(maxLa, maxLb, smemCand) * warpsPerBlock;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
-    iterate_post_kernel<false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, outHdr, outLines,
-                                                                             outOff, activeCount, maxLa, maxLb, smemCand, tune, in);
+    if (workCounter != nullptr && gridWarps > 0 && gridWarps < n)
+        iterate_post_kernel<false, true><<<gridWarps, 32, post_smem_per_warp(maxLa, maxLb, smemCand), stream>>>(
+            n, desc, state, arena, P, outHdr, outLines, outOff, activeCount, maxLa, maxLb, smemCand, tune, in, workCounter);
+    else
+        iterate_post_kernel<false, false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, outHdr, outLines, outOff,
+                                                                                 activeCount, maxLa, maxLb, smemCand, tune, in, nullptr);
     return cudaGetLastError();
 }
 
@@ -1198,8 +1232,8 @@ cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * stat
     DevParams P{};
     P.go = go; P.ge = ge;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
-    iterate_post_kernel<true><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, nullptr, nullptr,
-                                                                            nullptr, nullptr, maxLa, maxLb, 0, 0, DevInputs{});
+    iterate_post_kernel<true, false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, nullptr, nullptr,
+                                                                            nullptr, nullptr, maxLa, maxLb, 0, 0, DevInputs{}, nullptr);
     return cudaGetLastError();
 }
 

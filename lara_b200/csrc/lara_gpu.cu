@@ -78,6 +78,7 @@ struct Pilot
 struct Device
 {
     int id = 0;
+    int smCount = 148;
     cudaStream_t stream = nullptr;          // == workers[0].stream
     std::vector<Worker> workers;
     std::mutex queueMutex;
@@ -114,6 +115,8 @@ struct lara_ctx
     int bandMaxW = 1024;                    // widest band; beyond it the full-matrix kernel runs (env LARA_B200_BANDMAXW)
     int bandMinWarps = 400;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
     bool band24 = true;                     // 24-diagonal one-thread-per-pair shape (env LARA_B200_BAND24=0: off)
+    int postGridPerSm = 0;                  // > 0: post kernel as this many resident one-warp blocks per SM pulling pairs
+                                            // from a counter; < 0: that many warps in total (env LARA_B200_POSTGRID)
     int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
     bool fillPrio = false;                  // DP launches on high-priority streams (env LARA_B200_FILLPRIO)
     int verbose = 0;                        // env LARA_B200_VERBOSE=1: host-side stage times of every batch on stderr
@@ -621,9 +624,13 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     // two copies of the slot lists (the DP launches read one, a compaction writes the other) + one counter per class
     int32_t * dIdx = nullptr;
     size_t const idxStride = std::max<size_t>(idxAll.size(), 1);
-    CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * (2 * idxStride + cls.size() + 1), s));
+    int const nIter = ctx.P.num_iterations;
+    size_t const nCtr = ctx.postGridPerSm != 0 ? (size_t)nIter : 0;        // one work counter per post launch
+    CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * (2 * idxStride + cls.size() + 1 + nCtr), s));
     CK(cudaMemcpyAsync(dIdx, idxAll.data(), sizeof(int32_t) * idxAll.size(), cudaMemcpyHostToDevice, s));
     int32_t * const dCounts = dIdx + 2 * idxStride;
+    int32_t * const dPostCtr = nCtr ? dCounts + cls.size() + 1 : nullptr;
+    if (nCtr) CK(cudaMemsetAsync(dPostCtr, 0, sizeof(int32_t) * nCtr, s));
     std::vector<int> clsSide(cls.size(), 0), clsCount(cls.size());
     std::vector<int32_t> hCounts(cls.size());
     for (size_t k = 0; k < cls.size(); ++k) clsCount[k] = std::get<2>(cls[k]);
@@ -636,7 +643,6 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
     while (smemCand < maxK && smemCand < ctx.postSmemCand) smemCand <<= 1;
 
     // ---- the subgradient loop -------------------------------------------------------------------------------------
-    int const nIter = ctx.P.num_iterations;
     size_t const needEv = 2 + 3 * (size_t)nIter;
     while (wk.events.size() < needEv)
     {
@@ -669,7 +675,8 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         for (size_t k = auxBase; k < cls.size(); ++k) CK(cudaStreamWaitEvent(s, wk.auxJoin[k - auxBase], 0));
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 1], s));
         CK(launch_iterate_post(n, dDesc, dState, arena, dp, dv.dOutHdr + begin, dv.dOutLines, dv.dOutOff + begin,
-                               wk.dActive, maxLa, maxLb, smemCand, dv.in, s));
+                               wk.dActive, maxLa, maxLb, smemCand, dv.in, s, nCtr ? dPostCtr + it : nullptr,
+                               ctx.postGridPerSm > 0 ? ctx.postGridPerSm * dv.smCount : -ctx.postGridPerSm));
         wk.stats.kernel_launches += 1;
         CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 2], s));
         itersRun = it + 1;
@@ -924,6 +931,7 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_BANDMINWARPS")) ctx->bandMinWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BAND24")) ctx->band24 = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_BANDQ")) ctx->bandForceQ = std::atoi(e);
+    if (char const * e = std::getenv("LARA_B200_POSTGRID")) ctx->postGridPerSm = std::max(-4096, std::min(32, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_VERBOSE")) ctx->verbose = std::atoi(e);
     if (char const * e = std::getenv("LARA_B200_FILLPRIO")) ctx->fillPrio = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_COMPACT")) ctx->compactSlots = std::atoi(e) != 0;
@@ -972,6 +980,7 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
             CK(cudaEventCreate(&dv.evRun0));
             CK(cudaEventCreate(&dv.evRun1));
             CK(post_configure_device());
+            CK(cudaDeviceGetAttribute(&dv.smCount, cudaDevAttrMultiProcessorCount, id));
             // L2 fetch granularity (a hint; the driver default fetches 64 bytes per missed 32-byte sector): the post
             // kernel reads isolated 32-byte records, the fill reads whole lines either way.  LARA_B200_L2FETCH = 32|64|128
             if (char const * e = std::getenv("LARA_B200_L2FETCH"))

@@ -167,11 +167,12 @@ __host__ __device__ inline int64_t band_val_index(int bandW, int ppw, int slot, 
 {
     return (((int64_t)r * (bandW >> 2) + (x >> 2)) * ppw + slot) * 4 + (x & 3);
 }
-// traceback + valid_solution + matching + bounds + update for all n pairs of the batch
+// traceback + valid_solution + matching + bounds + update for all n pairs of the batch.  With a work counter (zero
+// before the launch) and gridWarps < n the grid is gridWarps one-warp blocks that pull pairs from the counter.
 cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                 DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
                                 int32_t * activeCount, int maxLa, int maxLb, int smemCand, DevInputs const & in,
-                                cudaStream_t stream);
+                                cudaStream_t stream, int32_t * workCounter = nullptr, int gridWarps = 0);
 // traceback only (unit entry point lara_gpu_gotoh_batch)
 cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                   int32_t go, int32_t ge, int maxLa, int maxLb, cudaStream_t stream);

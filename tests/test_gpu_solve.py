@@ -99,6 +99,8 @@ def test_solve_skewed_lengths(built):
     dict(LARA_B200_BANDMAXW="32", LARA_B200_BATCH="33"),
     dict(LARA_B200_BANDMINWARPS="1"),                   # lets the 24-diagonal one-thread shape in on a small batch
     dict(LARA_B200_BAND24="0", LARA_B200_BANDMINWARPS="1"),
+    dict(LARA_B200_POSTGRID="-7"),                      # post kernel as 7 resident warps pulling pairs from a counter
+    dict(LARA_B200_POSTGRID="-5", LARA_B200_WORKERS="2", LARA_B200_BATCH="40"),
 ])
 def test_solve_kernel_variants(built, env, monkeypatch):
     """Every DP kernel family and the scheduling switches give the same bits: full matrix, band blocks of 4 / 8 / 16
