@@ -50,7 +50,8 @@ def main():
     print("config %s: %d sequences, %d pairs" % (cfg, n, n * (n - 1) // 2))
     print("GPU CLI rc=%d wall %.2f s, %.0f pairs/s" % (cp.returncode, tg, n * (n - 1) / 2 / tg))
     err = cp.stderr.decode()
-    print("\n".join("   " + ln for ln in err.strip().split("\n")[-8:]))
+    keep = 100000 if os.environ.get("LARA_B200_VERBOSE") else 8          # verbose runs: the whole stage listing
+    print("\n".join("   " + ln for ln in err.strip().split("\n")[-keep:]))
     if cp.returncode != 0 or no_ref:
         return cp.returncode
     ref = os.path.join(ROOT, "oracle", "_ref", "lara_scalar")
