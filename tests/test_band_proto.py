@@ -24,6 +24,21 @@ def test_band_closed_forms_equal_full_matrix(seed):
         assert msg is None, "la=%d lb=%d band=[%d,%d] go=%d: %s" % (la, lb, dlo, dhi, go, msg)
 
 
+@pytest.mark.parametrize("seed", range(4))
+def test_sheared_band_closed_forms_equal_full_matrix(seed):
+    """Specification for the next band kernel: a band whose diagonals move right with the rows
+    (dlo[r], dhi[r] non-decreasing, shift < width) keeps the same closed forms for the gap regions: values, trace
+    decisions, end values and traceback lines equal the full matrix for pairs with lenA well above lenB."""
+    rng = np.random.default_rng(300 + seed)
+    for it in range(40):
+        lb = int(rng.integers(1, 30)); la = lb + int(rng.integers(0, 40))
+        dlo, dhi = bp.sheared_bounds(rng, la, lb, int(rng.integers(2, 10)))
+        go, ge = [(-49152, -16384), (-3 * 8192, -8192), (-20000, -19999)][it % 3]
+        alpha = None if it % 2 else [-16384, 0, 16384, 32768]
+        msg = bp.check_one(rng, la, lb, dlo, dhi, go, ge, float(rng.uniform(0.1, 0.95)), alpha)
+        assert msg is None, "la=%d lb=%d go=%d dlo=%s: %s" % (la, lb, go, list(dlo), msg)
+
+
 def test_band_walk_equals_oracle_gotoh(built):
     from oracle import binding as ob
     rng = np.random.default_rng(9)
