@@ -42,7 +42,7 @@ def main():
     seqs = [cat[off[i]:off[i + 1]] for i in range(len(off) - 1)]
     rng = np.random.default_rng(7)
     P = ob.default_params()
-    st, sh, cells_st, cells_sh = [], [], 0, 0
+    st, sh, cells_st, cells_sh, cells_p2, cells_full = [], [], 0, 0, 0, 0
     for _ in range(npairs):
         i, j = rng.choice(len(seqs), 2, replace=False)
         a, b = (seqs[i], seqs[j]) if len(seqs[i]) >= len(seqs[j]) else (seqs[j], seqs[i])
@@ -51,6 +51,8 @@ def main():
         st.append(s); sh.append(h)
         r32 = lambda w: max(32, (w + 31) // 32 * 32) if w > 24 else 24
         cells_st += r32(s) * len(b); cells_sh += r32(h) * len(b)
+        p2 = 24 if s <= 24 else 1 << int(np.ceil(np.log2(max(s, 32))))          # what choose_band takes today
+        cells_p2 += min(p2 * len(b), len(a) * len(b)); cells_full += len(a) * len(b)
     st, sh = np.array(st), np.array(sh)
     q = lambda x: "p10 %d  p50 %d  p90 %d  max %d" % tuple(np.percentile(x, [10, 50, 90, 100]).astype(int))
     print("%s, first %d sequences, %d random pairs" % (cfg, nseq, npairs))
@@ -58,6 +60,8 @@ def main():
     print("sheared band need:  ", q(sh))
     print("band cells per pair (widths rounded up to the kernels' 24 / 32 k): straight %.0f, sheared %.0f (%.2fx)"
           % (cells_st / npairs, cells_sh / npairs, cells_st / max(cells_sh, 1)))
+    print("today (24 or a power of two >= 32, full matrix when the band is not smaller): %.0f; full matrix: %.0f"
+          % (cells_p2 / npairs, cells_full / npairs))
 
 
 if __name__ == "__main__":
