@@ -124,7 +124,7 @@ typedef struct lara_stats
     double  ms_device;         /* CUDA-event span of the solve on the library's stream (max over devices) */
     int64_t reserved[7];       /* [0] concurrent workers per device, [1] pairs solved by the band kernels, [2] of those in
                                   blocks of 16 diagonals, [3] sum of their band widths, [4] algorithmic HBM bytes of the
-                                  DP launches, [5] DP cells actually computed (band cells), [6] unused */
+                                  DP launches, [5] DP cells actually computed (band cells), [6] batches run */
 } lara_stats;
 
 typedef struct lara_ctx lara_ctx;

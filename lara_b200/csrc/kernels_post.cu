@@ -729,10 +729,12 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         return;
     }
 
-    // per edge { seqScore, pv, ioff, degree }, per interaction { reverse index, partner cell, structScore, dual } and
-    // { partner edge, seqScore of the partner, owner, 0 }  (lara_gpu.cuh: offEdge, offInter)
+    // per edge { seqScore, pv, ioff, degree }; per interaction the hot record { reverse index, partner cell, structScore, dual }
+    // (16 bytes: the interactions of a row are neighbours, four to a 64-byte fetch) and, in an array of its own, the
+    // cold one { partner edge, seqScore of the partner, owner, 0 }  (lara_gpu.cuh: offEdge, offInter, offInterCold)
     int4 * __restrict__ edge = reinterpret_cast<int4 *>(arena + d.offEdge);
     int4 * __restrict__ inter = reinterpret_cast<int4 *>(arena + d.offInter);
+    int4 const * __restrict__ cold = reinterpret_cast<int4 const *>(arena + d.offInterCold);
     int32_t * __restrict__ list = arena + d.offList;
     // candidates are collected in shared memory when their upper bound fits, else in the pair's global buffer
     // (and moved to shared memory for the sort when the actual number fits)
@@ -805,8 +807,8 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         bool cycle = false;
         if (inSol)
         {
-            int4 const r1 = inter[2 * (size_t)x + 1];           // { partner edge, its seqScore, owner, 0 }
-            cycle = (r1.y + s + inter[2 * (size_t)rx].w == edge[r1.x].y);
+            int4 const r1 = cold[(size_t)x];           // { partner edge, its seqScore, owner, 0 }
+            cycle = (r1.y + s + inter[(size_t)rx].w == edge[r1.x].y);
         }
         if (!cycle) mark(x, rx);
     };
@@ -847,7 +849,7 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
                 os[u] = o;
                 xs[u] = __shfl_sync(kFull, er.z, o) + (t - __shfl_sync(kFull, off, o));
                 r0[u] = make_int4(0, 0, 0, 0);
-                if (t < total) r0[u] = inter[2 * (size_t)xs[u]];    // { reverse interaction, partner cell, structScore, dual }
+                if (t < total) r0[u] = inter[(size_t)xs[u]];    // { reverse interaction, partner cell, structScore, dual }
             }
             #pragma unroll
             for (int u = 0; u < kItems; ++u)
@@ -938,7 +940,7 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
             int4 rf = make_int4(0, 0, 0, 0);
             for (int x = er.z; x < er.z + er.w && found < 0 && !selfFirst; ++x)
             {
-                int4 const r0 = inter[2 * (size_t)x];
+                int4 const r0 = inter[(size_t)x];
                 if ((uint32_t)r0.y > myCell && sq == top) { selfFirst = true; break; }
                 if (sq + r0.z + r0.w == top) { found = x; rf = r0; }
             }
@@ -1007,7 +1009,7 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
     {
         uint32_t const x = (uint32_t)list[i];
         size_t const di = (size_t)(x & 0x7fffffffu);
-        int32_t * const dual = &reinterpret_cast<int32_t *>(inter + 2 * di)[3];
+        int32_t * const dual = &reinterpret_cast<int32_t *>(inter + di)[3];
         float const f = __int2float_rn(*dual);
         *dual = __float2int_rz((x >> 31) ? __fadd_rn(f, stepSize) : __fsub_rn(f, stepSize));
     }
@@ -1028,13 +1030,13 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
             for (int i = lane; i < nList; i += 32)
             {
                 size_t const di = (size_t)((uint32_t)list[i] & 0x7fffffffu);
-                int const l = inter[2 * di + 1].z;
+                int const l = cold[di].z;
                 int4 const er = edge[l];
                 int32_t const sq = er.x;
                 int32_t top = sq;
                 for (int x = er.z; x < er.z + er.w; ++x)
                 {
-                    int4 const r0 = inter[2 * (size_t)x];
+                    int4 const r0 = inter[(size_t)x];
                     top = max(top, sq + r0.z + r0.w);
                 }
                 reinterpret_cast<int32_t *>(edge + l)[1] = top;
@@ -1045,14 +1047,14 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         for (int k = lane; k < nPairs; k += 32)
         {
             size_t const di = (size_t)((uint32_t)list[2 * k] & 0x7fffffffu);
-            int const l = inter[2 * di + 1].z;              // owner of interaction di
+            int const l = cold[di].z;              // owner of interaction di
             int4 const er = edge[l];
             int32_t const sq = er.x;
             int32_t top = sq;
             #pragma unroll 4
             for (int x = er.z; x < er.z + er.w; ++x)
             {
-                int4 const r0 = inter[2 * (size_t)x];
+                int4 const r0 = inter[(size_t)x];
                 top = max(top, sq + r0.z + r0.w);
             }
             reinterpret_cast<int32_t *>(edge + l)[1] = top;
@@ -1061,8 +1063,8 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         for (int k = lane; k < nPairs; k += 32)
         {
             size_t const di = (size_t)((uint32_t)list[2 * k + 1] & 0x7fffffffu);
-            int4 const r0 = inter[2 * di];
-            int const l = inter[2 * di + 1].z;
+            int4 const r0 = inter[di];
+            int const l = cold[di].z;
             int32_t const v = edge[l].x + r0.z + r0.w;
             atomicMax(&reinterpret_cast<int32_t *>(edge + l)[1], v);
             atomicMax(&vals[perm[l]], v);
@@ -1155,6 +1157,8 @@ size_t post_smem_per_warp(int maxLa, int maxLb, int smemCand)
 }
 
 } // namespace
+
+size_t post_smem_bytes_per_warp(int maxLa, int maxLb, int smemCand) { return post_smem_per_warp(maxLa, maxLb, smemCand); }
 
 // opt in to the full shared memory carve-out for both instantiations (per device, at context creation)
 cudaError_t post_configure_device()

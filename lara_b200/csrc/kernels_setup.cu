@@ -448,11 +448,12 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
         ptr += R;
     }
     }
-    // 4. records of the iteration kernel (lara_gpu.cuh: offEdge, offInter)
+    // 4. records of the iteration kernel (lara_gpu.cuh: offEdge, offInter, offInterCold)
     __syncwarp();
     {
         int4 * __restrict__ edge = reinterpret_cast<int4 *>(arena + d.offEdge);
         int4 * __restrict__ inter = reinterpret_cast<int4 *>(arena + d.offInter);
+        int4 * __restrict__ cold = reinterpret_cast<int4 *>(arena + d.offInterCold);
         for (int e = lane; e < E; e += 32)
         {
             int const x0 = ioff[e], x1 = ioff[e + 1];
@@ -465,8 +466,8 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
             for (int x = x0; x < x1; ++x)
             {
                 int const m = part[x];
-                inter[2 * (size_t)x] = make_int4(rev[x], ppos[x], sc[x], 0);
-                inter[2 * (size_t)x + 1] = make_int4(m, seqScore[m], e, 0);
+                inter[(size_t)x] = make_int4(rev[x], ppos[x], sc[x], 0);
+                cold[(size_t)x] = make_int4(m, seqScore[m], e, 0);
             }
         }
     }

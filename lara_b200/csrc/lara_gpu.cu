@@ -79,6 +79,7 @@ struct Device
 {
     int id = 0;
     int smCount = 148;
+    int smemOptin = 0;                      // cudaDevAttrMaxSharedMemoryPerBlockOptin
     cudaStream_t stream = nullptr;          // == workers[0].stream
     std::vector<Worker> workers;
     std::mutex queueMutex;
@@ -98,6 +99,7 @@ struct Device
     int64_t outLinesTotal = 0;
     lara_stats stats{};
     std::string err;
+    bool poolHeld = false;                  // counted in g_poolUsers
 };
 
 } // namespace
@@ -130,7 +132,8 @@ struct lara_ctx
     int64_t nPrepared = 0;
     bool prepared = false, ran = false;
     lara_stats stats{};
-    size_t batchPairsCap = 0;               // test hook: max pairs per batch (0 = automatic)
+    size_t batchPairsCap = 0;               // test hook: max pairs per batch, 0 = automatic (env LARA_B200_BATCHCAP)
+    size_t workerMinPairs = 2048;           // a device runs one worker per this many pairs, up to nWorkers (env LARA_B200_WORKERPAIRS)
 };
 
 namespace
@@ -560,7 +563,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         return;
     }
     int64_t sizeC = 0;
-    for (int i = 0; i < n; ++i) sizeC += 14 * align4(std::max(desc[(size_t)i].D, 1)) + 8 + align4(std::max(desc[(size_t)i].nVals, 1));
+    for (int i = 0; i < n; ++i) sizeC += 14 * align4(std::max(desc[(size_t)i].D, 1)) + 20 + align4(std::max(desc[(size_t)i].nVals, 1));
     Region rC;
     region_alloc(rC, sizeC, al256(sizeA) + al256(sizeB));
     lap("alloc C");
@@ -570,8 +573,9 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         PairDesc & d = desc[(size_t)i];
         d.offPart = rC.take(d.D); d.offPpos = rC.take(d.D); d.offSc = rC.take(d.D); d.offDual = rC.take(d.D);
         d.offRev = rC.take(d.D); d.offList = rC.take(d.D); d.offVals = rC.take(d.nVals);
-        rC.used = (rC.used + 7) & ~(int64_t)7;            // 32-byte records
-        d.offInter = rC.take(8ll * d.D);
+        rC.used = (rC.used + 15) & ~(int64_t)15;          // hot records: rows start on 64-byte fetch units where they can
+        d.offInter = rC.take(4ll * d.D);
+        d.offInterCold = rC.take(4ll * d.D);
         wk.stats.n_active_edges += d.E; wk.stats.n_interactions += d.D;
         wk.stats.filter_cells += 2ll * d.la * d.lb;
     }
@@ -732,6 +736,7 @@ void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t en
         wk.stats.ms_bounds += ev_ms(wk.events[2 + 3 * (size_t)it + 1], wk.events[2 + 3 * (size_t)it + 2]);
     }
     wk.stats.n_pairs += n;
+    wk.stats.reserved[6] += 1;                                  // batches run
     CK(cudaFreeAsync(dIdx, s));
     for (void * f : fallback) CK(cudaFreeAsync(f, s));
     CK(cudaFreeAsync(dState, s));
@@ -813,8 +818,9 @@ void run_device(lara_ctx & ctx, Device & dv)
     {
         CK(cudaSetDevice(dv.id));
         std::memset(&dv.stats, 0, sizeof(dv.stats));
+        dv.err.clear();
         // few pairs: one worker is enough (and keeps the small-case latency low)
-        int nW = (int)std::min<size_t>((size_t)ctx.nWorkers, (dv.pairs.size() + 2047) / 2048);
+        int nW = (int)std::min<size_t>((size_t)ctx.nWorkers, (dv.pairs.size() + ctx.workerMinPairs - 1) / ctx.workerMinPairs);
         nW = std::max(1, std::min(nW, (int)dv.workers.size()));
         dv.nextBegin = 0;
         for (Worker & wk : dv.workers) { std::memset(&wk.stats, 0, sizeof(wk.stats)); wk.err.clear(); }
@@ -863,6 +869,7 @@ void run_device(lara_ctx & ctx, Device & dv)
             dv.stats.reserved[3] += dv.workers[(size_t)w].stats.reserved[3];
             dv.stats.reserved[4] += dv.workers[(size_t)w].stats.reserved[4];
             dv.stats.reserved[5] += dv.workers[(size_t)w].stats.reserved[5];
+            dv.stats.reserved[6] += dv.workers[(size_t)w].stats.reserved[6];
         }
     }
     catch (std::exception const & e)
@@ -870,6 +877,20 @@ void run_device(lara_ctx & ctx, Device & dv)
         dv.err = e.what();
         cudaGetLastError();
     }
+}
+
+// contexts per device that rely on the raised release threshold of the device's default memory pool
+std::mutex g_poolMutex;
+std::map<int, int> g_poolUsers;
+void pool_acquire(int dev) { std::lock_guard<std::mutex> lock(g_poolMutex); ++g_poolUsers[dev]; }
+bool pool_release(int dev)
+{
+    std::lock_guard<std::mutex> lock(g_poolMutex);
+    auto it = g_poolUsers.find(dev);
+    if (it == g_poolUsers.end()) return false;
+    if (--it->second > 0) return false;
+    g_poolUsers.erase(it);
+    return true;
 }
 
 int set_err(lara_ctx * ctx, int code, std::string const & msg)
@@ -937,6 +958,8 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_COMPACT")) ctx->compactSlots = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_SMEMCAND")) ctx->postSmemCand = std::max(32, std::min(2048, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
+    if (char const * e = std::getenv("LARA_B200_BATCHCAP")) ctx->batchPairsCap = (size_t)std::max(0, std::atoi(e));
+    if (char const * e = std::getenv("LARA_B200_WORKERPAIRS")) ctx->workerMinPairs = (size_t)std::max(1, std::atoi(e));
     ctx->P = *params;
     ctx->dp = make_dev_params(*params);
     try
@@ -981,6 +1004,7 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
             CK(cudaEventCreate(&dv.evRun1));
             CK(post_configure_device());
             CK(cudaDeviceGetAttribute(&dv.smCount, cudaDevAttrMultiProcessorCount, id));
+            CK(cudaDeviceGetAttribute(&dv.smemOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, id));
             // L2 fetch granularity (a hint; the driver default fetches 64 bytes per missed 32-byte sector): the post
             // kernel reads isolated 32-byte records, the fill reads whole lines either way.  LARA_B200_L2FETCH = 32|64|128
             if (char const * e = std::getenv("LARA_B200_L2FETCH"))
@@ -991,11 +1015,13 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
                 cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
                 if (ctx->verbose) std::fprintf(stderr, "[lara_b200] dev %d L2 fetch granularity %zu\n", id, got);
             }
-            // keep freed blocks in the stream-ordered pool between batches
+            // keep freed blocks in the stream-ordered pool between batches (undone by the last lara_gpu_destroy)
             cudaMemPool_t pool;
             CK(cudaDeviceGetDefaultMemPool(&pool, id));
             uint64_t thr = UINT64_MAX;
             CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+            pool_acquire(id);
+            dv.poolHeld = true;
         }
     }
     catch (std::exception const & ex)
@@ -1015,6 +1041,19 @@ void lara_gpu_destroy(lara_ctx * ctx)
     {
         cudaSetDevice(dv.id);
         for (Worker & wk : dv.workers) if (wk.stream) cudaStreamSynchronize(wk.stream);
+        if (dv.poolHeld && pool_release(dv.id))
+        {
+            // the stream-ordered pool kept freed blocks between batches (lara_gpu_create); this was the last context
+            // on the device: give them back and restore the default threshold
+            cudaMemPool_t pool;
+            if (cudaDeviceGetDefaultMemPool(&pool, dv.id) == cudaSuccess)
+            {
+                uint64_t thr = 0;
+                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+                cudaMemPoolTrimTo(pool, 0);
+            }
+            cudaGetLastError();
+        }
         device_free_inputs(dv);
         device_free_outputs(dv);
         cudaFree(dv.negBuf);
@@ -1044,11 +1083,12 @@ int lara_gpu_set_sequences(lara_ctx * ctx, int32_t n_seq, uint8_t const * seq_ca
     if (n_seq < 0 || !seq_off || !bp_off) return set_err(ctx, LARA_E_INVALID, "null argument");
     int64_t const total = seq_off[n_seq];
     int64_t const nnz = bp_off[total];
+    if (total > 0 && !seq_cat) return set_err(ctx, LARA_E_INVALID, "null argument: seq_cat");
+    if (nnz > 0 && (!bp_partner || !bp_weight)) return set_err(ctx, LARA_E_INVALID, "null argument: bp_partner / bp_weight");
     for (int32_t i = 0; i < n_seq; ++i)
     {
         int64_t const L = seq_off[i + 1] - seq_off[i];
         if (L < 1) return set_err(ctx, LARA_E_INVALID, "empty sequence");
-        if (L > 32 * kMaxR && false) return set_err(ctx, LARA_E_UNSUPPORTED, "sequence too long");
         if (L > 32767) return set_err(ctx, LARA_E_UNSUPPORTED, "sequences longer than 32767 nt are not supported");
         for (int64_t g = seq_off[i]; g < seq_off[i + 1]; ++g)
         {
@@ -1056,6 +1096,19 @@ int lara_gpu_set_sequences(lara_ctx * ctx, int32_t n_seq, uint8_t const * seq_ca
             for (int64_t x = bp_off[g]; x < bp_off[g + 1]; ++x)
                 if (bp_partner[x] < 0 || bp_partner[x] >= L) return set_err(ctx, LARA_E_INVALID, "base pair partner out of range");
         }
+        // the adjacency is that of an undirected graph (src/lagrange.hpp:130-138): every base pair listed once from
+        // each end with the same weight; the candidate buffer of the matching is sized from that
+        for (int64_t g = seq_off[i]; g < seq_off[i + 1]; ++g)
+            for (int64_t x = bp_off[g]; x < bp_off[g + 1]; ++x)
+            {
+                int64_t const h = seq_off[i] + bp_partner[x];
+                int back = 0;
+                for (int64_t y = bp_off[h]; y < bp_off[h + 1]; ++y)
+                    if (seq_off[i] + bp_partner[y] == g) { ++back; if (bp_weight[y] != bp_weight[x]) back = -1000; }
+                if (h == g || back != 1)
+                    return set_err(ctx, LARA_E_INVALID, "base pair adjacency is not symmetric and duplicate-free (sequence " +
+                                                        std::to_string(i) + ", position " + std::to_string(g - seq_off[i]) + ")");
+            }
     }
     ctx->nSeq = n_seq;
     ctx->seqOff.assign(seq_off, seq_off + n_seq + 1);
@@ -1122,6 +1175,17 @@ int lara_gpu_prepare_pairs(lara_ctx * ctx, int64_t n_pairs, int32_t const * idx_
             return set_err(ctx, LARA_E_UNSUPPORTED, "shorter sequence of a pair exceeds " + std::to_string(32 * kMaxR) +
                                                      " nt (single-pass DP limit; the band kernels are switched off)");
     }
+    {
+        // the post kernel keeps the lines of a pair in shared memory (kernels_post.cu: WarpSmem)
+        int maxLa = 0, maxLb = 0;
+        for (OrientedPair const & op : all) { maxLa = std::max(maxLa, op.la); maxLb = std::max(maxLb, op.lb); }
+        for (Device const & dv : ctx->devs)
+            if (n_pairs > 0 && post_smem_bytes_per_warp(maxLa, maxLb, 32) > (size_t)dv.smemOptin)
+                return set_err(ctx, LARA_E_UNSUPPORTED, "a pair of " + std::to_string(maxLa) + " x " + std::to_string(maxLb) +
+                               " nt needs " + std::to_string(post_smem_bytes_per_warp(maxLa, maxLb, 32)) +
+                               " bytes of shared memory per warp in the iteration kernel, the device offers " +
+                               std::to_string(dv.smemOptin));
+    }
     // longest first, like the reference's queue (CompareSeqLength, src/io.hpp:352-365)
     std::stable_sort(all.begin(), all.end(), [](OrientedPair const & x, OrientedPair const & y) {
         return x.la != y.la ? x.la > y.la : x.lb > y.lb;
@@ -1160,6 +1224,7 @@ int lara_gpu_run_prepared(lara_ctx * ctx)
 {
     if (!ctx) return LARA_E_INVALID;
     if (!ctx->prepared) return set_err(ctx, LARA_E_INVALID, "no prepared pairs");
+    ctx->ran = false;
     auto const t0 = std::chrono::steady_clock::now();
     if (ctx->devs.size() == 1)
         run_device(*ctx, ctx->devs[0]);
@@ -1172,9 +1237,14 @@ int lara_gpu_run_prepared(lara_ctx * ctx)
     double const ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     lara_stats agg{};
     agg.ms_h2d = ctx->stats.ms_h2d; agg.h2d_bytes = ctx->stats.h2d_bytes;
+    {
+        std::string all;
+        for (Device & dv : ctx->devs)
+            if (!dv.err.empty()) { all += (all.empty() ? "" : "; ") + ("device " + std::to_string(dv.id) + ": " + dv.err); dv.err.clear(); }
+        if (!all.empty()) return set_err(ctx, LARA_E_CUDA, all);
+    }
     for (Device & dv : ctx->devs)
     {
-        if (!dv.err.empty()) { std::string e = dv.err; dv.err.clear(); return set_err(ctx, LARA_E_CUDA, e); }
         agg.ms_setup = std::max(agg.ms_setup, dv.stats.ms_setup);
         agg.ms_dp = std::max(agg.ms_dp, dv.stats.ms_dp);
         agg.ms_bounds = std::max(agg.ms_bounds, dv.stats.ms_bounds);
@@ -1189,6 +1259,7 @@ int lara_gpu_run_prepared(lara_ctx * ctx)
         agg.reserved[3] += dv.stats.reserved[3];                               // sum of the band widths
         agg.reserved[4] += dv.stats.reserved[4];                               // algorithmic HBM bytes of the DP launches
         agg.reserved[5] += dv.stats.reserved[5];                               // DP cells actually computed
+        agg.reserved[6] += dv.stats.reserved[6];                               // batches run
     }
     agg.ms_total = ms;
     ctx->stats = agg;
@@ -1280,6 +1351,9 @@ int lara_gpu_fetch_prepared(lara_ctx * ctx, lara_results * out)
     }
     catch (std::exception const & ex)
     {
+        // device-to-host copies into the block may still be in flight
+        for (Device & dv : ctx->devs) { cudaSetDevice(dv.id); cudaStreamSynchronize(dv.stream); }
+        cudaGetLastError();
         delete own;
         return set_err(ctx, LARA_E_CUDA, ex.what());
     }

@@ -78,8 +78,8 @@ struct PairDesc
     // records read by the iteration kernel (written at the end of the set-up from the arrays above, which stay
     // as the build-time form; pv and dual live only here afterwards):
     int64_t offEdge;            // per edge, 16 bytes: { seqScore, pv (queue top == pssm value), ioff, degree }   [E]
-    int64_t offInter;           // per interaction, 32 bytes: { reverse index, partner cell, structScore, dual,
-                                //                               partner edge, seqScore of the partner, owner edge, 0 }  [D]
+    int64_t offInter;           // per interaction, 16 bytes (hot): { reverse index, partner cell, structScore, dual }  [D]
+    int64_t offInterCold;       // per interaction, 16 bytes (cold): { partner edge, seqScore of the partner, owner edge, 0 }  [D]
     int64_t offRowRec;          // bands of <= 32 diagonals, per row a of the bitmap, 16 bytes: { id of the row's first edge,
                                 //   activity bits of b = a - dHi .. a - dHi + 31, of those the cells with interactions, 0 }   [la]   (0: not present)
     int64_t offLines;           // current lines  (a << 16) | b  [lb]
@@ -179,6 +179,8 @@ cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * stat
 // result gather: the used part of every pair's output slot -> dense posLow / posHigh / weight arrays at dstOff[q]
 cudaError_t launch_pack_lines(int n, PairOutHdr const * hdr, int32_t const * outLines, int64_t const * outOff,
                               int64_t const * dstOff, int32_t * low, int32_t * high, int32_t * weight, cudaStream_t stream);
+// dynamic shared memory one warp of the post kernels needs for pairs up to maxLa x maxLb
+size_t post_smem_bytes_per_warp(int maxLa, int maxLb, int smemCand);
 // per-device one-time configuration of the post kernels (shared memory opt-in)
 cudaError_t post_configure_device();
 // set-up stage 1: edge filter -> bitmap, optimum score, E

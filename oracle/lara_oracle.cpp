@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <set>
@@ -353,6 +354,8 @@ struct Lagrange
     std::vector<uint8_t> bestMatched;   // edgeMatching.count(idx) per best line
     std::vector<uint8_t> inSol;
     std::vector<int64_t> list;          // subgradientIndices
+    // developer statistics (LARA_ORACLE_STATS=1): sums over the iterations of one pair
+    int64_t stLines = 0, stWork = 0, stItems = 0, stList = 0, stCand = 0, stRescan = 0;
 
     inline ScoreType key(int32_t e, int64_t i) const { return seqScore[e] + sc[i] + dual[i]; }
 
@@ -441,6 +444,8 @@ struct Lagrange
             inSol[cur[k]] = 1;
         }
         list.clear();
+        stLines += (int64_t)cur.size();
+        for (int32_t idx : cur) { stWork += ioff[idx + 1] > ioff[idx]; stItems += ioff[idx + 1] - ioff[idx]; }
         for (int32_t idx : cur)                                                        // :344-374
         {
             ScoreType top = pv[idx];
@@ -482,6 +487,7 @@ struct Lagrange
                         q.emplace_back(-2 * sc[i], (int64_t)cellOf[line], (int64_t)cellOf[part[i]]);
             std::sort(q.begin(), q.end());
             q.erase(std::unique(q.begin(), q.end()), q.end());
+            stCand += (int64_t)q.size();
             auto lineOfCell = [&](int64_t cell) { return lineOfA[cell / lb]; };
             lowerBound += greedy_matching(q, (size_t)P->matching,
                 [&](int64_t l, int64_t r) { matched[lineOfCell(l)] = 1; matched[lineOfCell(r)] = 1; },
@@ -524,10 +530,12 @@ struct Lagrange
     // updateScores, :312-323
     void update_scores()
     {
+        stList += (int64_t)list.size();
         for (int64_t d : list)
         {
             // row owner of entry d: the reverse entry's partner
             int32_t l = part[rev[d]];
+            stRescan += ioff[l + 1] - ioff[l];
             pv[l] = rowTop(l);
             pssm[cellOf[l]] = pv[l];
         }
@@ -585,6 +593,14 @@ void solve_pair(lara_params const * P, SeqView const & sa, SeqView const & sb, i
         if (bestUpper == bestLower || remaining == 0u)
             break;
         lag.update_scores();
+    }
+    if (std::getenv("LARA_ORACLE_STATS"))
+    {
+        double const it = (double)(P->num_iterations - (int32_t)remaining);
+        std::fprintf(stderr, "[oracle] pair %d %d la %d lb %d E %zu D %lld iterations %.0f per iteration: lines %.1f with-interactions %.1f "
+                             "interactions-of-lines %.1f list %.1f candidates %.1f rescanned %.1f\n", idxFirst, idxSecond, lag.la, lag.lb,
+                     lag.cellOf.size(), (long long)lag.dimension(), it, lag.stLines / it, lag.stWork / it, lag.stItems / it,
+                     lag.stList / it, lag.stCand / it, lag.stRescan / it);
     }
     // getStructureLines, src/lagrange.hpp:437-487
     bool swapIdx = idxFirst > idxSecond;

@@ -112,6 +112,24 @@ def test_solve_kernel_variants(built, env, monkeypatch):
     assert util.results_equal(got, want) is None, util.results_equal(got, want)
 
 
+@pytest.mark.parametrize("env,workers", [
+    (dict(LARA_B200_BATCHCAP="30", LARA_B200_WORKERPAIRS="60"), 2),
+    (dict(LARA_B200_BATCHCAP="24", LARA_B200_WORKERPAIRS="40", LARA_B200_WORKERS="3", LARA_B200_COMPACT="1"), 3),
+    (dict(LARA_B200_BATCHCAP="50", LARA_B200_WORKERPAIRS="1000"), 1),
+])
+def test_solve_many_batches_per_worker(built, env, workers, monkeypatch):
+    """Concurrent workers that each run several batches through their reused slab (the configuration behind the
+    headline numbers: C3 = 4 batches on 2 workers): 231 pairs in batches of 24..50 on 1..3 workers."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    files = util.make_input(seed=43, n=22, length=70, lenmax=150)
+    got, want, st = _solve_both(files, num_iterations=60, max_nondecreasing=8)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+    assert st.reserved[0] == workers
+    assert st.reserved[6] >= 231 // int(env["LARA_B200_BATCHCAP"])          # batches run
+    assert st.reserved[6] >= 3 * workers
+
+
 def _solve_store(store, **kw):
     import lara_b200 as lb
     from oracle import binding as ob
