@@ -157,6 +157,132 @@ int read_dbn(std::istream & in, std::vector<Record> & out)
     return LARA_OK;
 }
 
+// ---- bpseq: SeqAn:rna_io/bpseq_read_write.h:81-159 ------------------------------------------------------------------
+// Records follow each other; each starts with '#' lines (the first one is the name, the others are comments) and
+// continues with "index nucleotide partner" lines up to the next '#' line.  An edge of weight 1 is added on the
+// line of the higher index (:139-140); the first index of a record is its offset.
+int read_bpseq(std::istream & in, std::vector<Record> & out)
+{
+    std::string line;
+    bool have = false;
+    auto next = [&]() -> bool
+    {
+        while (std::getline(in, line)) { rstrip(line); size_t p = line.find_first_not_of(" \t"); if (p != std::string::npos) { line = line.substr(p); return true; } }
+        return false;
+    };
+    have = next();
+    while (have)
+    {
+        Record rec;
+        bool named = false;
+        while (have && line[0] == '#')
+        {
+            size_t p = line.find_first_not_of(" \t", 1);
+            if (!named) { rec.name = p == std::string::npos ? std::string() : line.substr(p); named = !rec.name.empty(); }
+            have = next();
+        }
+        Graph g;
+        long offset = -1, cur = 0;
+        std::string raw;
+        while (have && line[0] != '#')
+        {
+            std::vector<std::string> t = split_ws(line);
+            if (t.size() < 3) return fail(LARA_E_IO, "bpseq: expected 'index nucleotide partner'");
+            if (offset < 0)
+            {
+                char * end = nullptr;
+                offset = std::strtol(t[0].c_str(), &end, 10);
+                if (!end || *end || offset < 0) return fail(LARA_E_IO, "bpseq: bad index '" + t[0] + "'");
+                cur = offset;
+            }
+            else
+                ++cur;
+            raw.push_back(t[1][0]);
+            char * end = nullptr;
+            long const pr = std::strtol(t[2].c_str(), &end, 10);
+            if (!end || *end || pr < 0) return fail(LARA_E_IO, "bpseq: bad partner '" + t[2] + "'");
+            if (pr != 0 && cur > pr)
+            {
+                if (pr < offset) return fail(LARA_E_IO, "bpseq: partner before the first index");
+                g.edges.push_back(Edge{(int32_t)(pr - offset), (int32_t)(cur - offset), 1.0});
+            }
+            have = next();
+        }
+        if (raw.empty()) return fail(LARA_E_IO, "bpseq: record without nucleotides");
+        rec.seq = to_rna5_string(raw);
+        rec.fixedGraphs.push_back(g);
+        out.push_back(rec);
+    }
+    return LARA_OK;
+}
+
+// ---- connect (.ct): SeqAn:rna_io/connect_read_write.h:112-213 --------------------------------------------------------
+// "N [ENERGY = e] name" then N lines "index nucleotide index-1 index+1 partner index"; edge of weight 1 on the line of
+// the higher index.
+int read_ct(std::istream & in, std::vector<Record> & out)
+{
+    std::string line;
+    auto next = [&]() -> bool
+    {
+        while (std::getline(in, line)) { rstrip(line); if (line.find_first_not_of(" \t") != std::string::npos) return true; }
+        return false;
+    };
+    while (next())
+    {
+        Record rec;
+        size_t p = line.find_first_not_of(" \t");
+        size_t q = line.find_first_of(" \t", p);
+        std::string const nStr = line.substr(p, q == std::string::npos ? std::string::npos : q - p);
+        char * end = nullptr;
+        long const n = std::strtol(nStr.c_str(), &end, 10);
+        if (!end || *end || n < 1) return fail(LARA_E_IO, "ct: bad sequence length '" + nStr + "'");
+        // second token up to white space or '=' (:131-148)
+        p = q == std::string::npos ? std::string::npos : line.find_first_not_of(" \t", q);
+        if (p != std::string::npos)
+        {
+            q = line.find_first_of(" \t=", p);
+            std::string tok = line.substr(p, q == std::string::npos ? std::string::npos : q - p);
+            if (tok.compare(0, 6, "ENERGY") == 0)
+            {
+                size_t eq = line.find('=', p);
+                size_t e0 = eq == std::string::npos ? std::string::npos : line.find_first_not_of(" \t", eq + 1);
+                size_t e1 = e0 == std::string::npos ? std::string::npos : line.find_first_of(" \t", e0);
+                size_t nm = e1 == std::string::npos ? std::string::npos : line.find_first_not_of(" \t", e1);
+                rec.name = nm == std::string::npos ? std::string() : line.substr(nm);
+            }
+            else
+                rec.name = tok + (q == std::string::npos ? std::string() : line.substr(q));
+        }
+        Graph g;
+        std::string raw;
+        long offset = 1;
+        for (long k = 0; k < n; ++k)
+        {
+            if (!next()) return fail(LARA_E_IO, "ct: record ends after " + std::to_string(k) + " of " + std::to_string(n) + " lines");
+            std::vector<std::string> t = split_ws(line);
+            if (t.size() < 5) return fail(LARA_E_IO, "ct: expected 'index nucleotide prev next partner index'");
+            if (k == 0)
+            {
+                offset = std::strtol(t[0].c_str(), &end, 10);
+                if (!end || *end) return fail(LARA_E_IO, "ct: bad index '" + t[0] + "'");
+            }
+            long const cur = offset + k;
+            raw += t[1];
+            long const pr = std::strtol(t[4].c_str(), &end, 10);
+            if (!end || *end || pr < 0) return fail(LARA_E_IO, "ct: bad partner '" + t[4] + "'");
+            if (pr != 0 && cur > pr)
+            {
+                if (pr < offset) return fail(LARA_E_IO, "ERROR: Incompatible pairing position in input file.");
+                g.edges.push_back(Edge{(int32_t)(pr - offset), (int32_t)(cur - offset), 1.0});
+            }
+        }
+        rec.seq = to_rna5_string(raw);
+        rec.fixedGraphs.push_back(g);
+        out.push_back(rec);
+    }
+    return LARA_OK;
+}
+
 // ---- extended bpseq: SeqAn:rna_io/ebpseq_read_write.h:112-165 (header), :173-395 (records) ----
 int read_ebpseq(std::istream & in, std::vector<Record> & out)
 {
@@ -352,6 +478,11 @@ int lara_input_read_file(lara_input * in, char const * path)
     std::string p(path);
     if (ends_with(p, ".ebpseq")) return read_ebpseq(f, in->recs);
     if (ends_with(p, ".dbn")) return read_dbn(f, in->recs);
+    if (ends_with(p, ".bpseq")) return read_bpseq(f, in->recs);
+    if (ends_with(p, ".ct")) return read_ct(f, in->recs);
+    // .sth (Stockholm) is not read: SeqAn's reader fills only record.align and leaves record.sequence empty
+    // (SeqAn:rna_io/stockholm_read_write.h:253-264), so the reference itself cannot align such input; .dbv (Vienna
+    // without names) is not read either.  Everything else is treated as a sequence file, like src/io.hpp:154-199.
     return read_fasta(f, in->recs);
 }
 

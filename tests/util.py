@@ -60,7 +60,9 @@ def golden_setup(case):
             argv += ["-d", f]
     else:
         argv += ["-i", files[0]]
-    argv += list(case["options"])
+    if case.get("ref_file"):
+        argv += ["-r", os.path.join(GOLDEN, case["ref_file"])]
+    argv += [os.path.join(GOLDEN, o[len("@golden/"):]) if o.startswith("@golden/") else o for o in case["options"]]
     if case["build"] == "simd":
         argv += ["-g", "1"]
     p = lb.Parameters(argv)

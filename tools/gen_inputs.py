@@ -181,6 +181,48 @@ def write_dbn(path, recs):
             f.write(">%s\n%s\n%s\n" % (name, s, dotbracket(len(s), pairs)))
 
 
+def _one_partner_pairs(L, pairs):
+    """pairs in which every position occurs at most once (bpseq / ct hold one partner per base)"""
+    used = set()
+    out = []
+    for i, j in sorted(pairs):
+        if i in used or j in used or not (0 <= i < j < L):
+            continue
+        used.add(i)
+        used.add(j)
+        out.append((i, j))
+    return out
+
+
+def write_bpseq(path, recs):
+    """SeqAn rna_io/bpseq_read_write.h: '# name' then 'index nucleotide partner' lines (0 = unpaired)."""
+    with open(path, "w") as f:
+        for name, s, pairs in recs:
+            partner = {}
+            for i, j in _one_partner_pairs(len(s), pairs):
+                partner[i] = j
+                partner[j] = i
+            f.write("# %s\n" % name)
+            for i, c in enumerate(s):
+                f.write("%d %s %d\n" % (i + 1, c, partner.get(i, -1) + 1))
+
+
+def write_ct(path, recs):
+    """SeqAn rna_io/connect_read_write.h: 'N [ENERGY = e] name' then 'index nucleotide index-1 index+1 partner index'."""
+    with open(path, "w") as f:
+        for k, (name, s, pairs) in enumerate(recs):
+            partner = {}
+            for i, j in _one_partner_pairs(len(s), pairs):
+                partner[i] = j
+                partner[j] = i
+            if k % 2 == 0:
+                f.write("%d\tENERGY = -%d.5\t%s\n" % (len(s), 10 + k, name))
+            else:
+                f.write("%5d %s\n" % (len(s), name))
+            for i, c in enumerate(s):
+                f.write("%5d %s %5d %5d %5d %5d\n" % (i + 1, c, i, (i + 2) if i + 1 < len(s) else 0, partner.get(i, -1) + 1, i + 1))
+
+
 def write_fasta(path, recs):
     with open(path, "w") as f:
         for name, s, _ in recs:
@@ -239,6 +281,14 @@ def generate(outdir, seed, n, length, fmt, lenmax=0, related=True, skew=False):
     if fmt == "ebpseq":
         p = os.path.join(outdir, "input.ebpseq")
         write_ebpseq(p, recs, rng)
+        return [p]
+    if fmt == "bpseq":
+        p = os.path.join(outdir, "input.bpseq")
+        write_bpseq(p, recs)
+        return [p]
+    if fmt == "ct":
+        p = os.path.join(outdir, "input.ct")
+        write_ct(p, recs)
         return [p]
     if fmt == "fasta":
         p = os.path.join(outdir, "input.fasta")
