@@ -122,9 +122,14 @@ typedef struct lara_stats
     int64_t n_active_edges;    /* sum of E                                              */
     int64_t n_interactions;    /* sum of D (dual dimension)                             */
     double  ms_device;         /* CUDA-event span of the solve on the library's stream (max over devices) */
-    int64_t reserved[7];       /* [0] concurrent workers per device, [1] pairs solved by the band kernels, [2] of those in
+    int64_t reserved[16];      /* [0] concurrent workers per device, [1] pairs solved by the band kernels, [2] of those in
                                   blocks of 16 diagonals, [3] sum of their band widths, [4] algorithmic HBM bytes of the
-                                  DP launches, [5] DP cells actually computed (band cells), [6] batches run */
+                                  DP launches, [5] DP cells actually computed (band cells), [6] batches run,
+                                  [7] iteration steps run (one DP launch + one post launch each), [8] pair slots of the
+                                  DP launches, summed over the steps, [9] of those the slots whose pair was still
+                                  iterating (live-lane fraction = [9] / [8]), [10] algorithmic HBM bytes of ONE DP launch
+                                  with every pair of the first batch live, [11] pairs of that launch, [12] pairs taken
+                                  into freed slots of a running batch (slot refill), [13..15] unused */
 } lara_stats;
 
 typedef struct lara_ctx lara_ctx;

@@ -75,7 +75,7 @@ class LaraStats(C.Structure):
         ("n_active_edges", C.c_int64),
         ("n_interactions", C.c_int64),
         ("ms_device", C.c_double),
-        ("reserved", C.c_int64 * 7),
+        ("reserved", C.c_int64 * 16),
     ]
 
 

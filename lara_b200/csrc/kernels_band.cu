@@ -38,10 +38,12 @@
 //
 // Memory: position specific scores come from a dense band array vals[row][diagonal], stored in 16-byte chunks of 4
 // diagonals and interleaved over the pairs of a warp ([row][chunk][pair slot]) so that a warp-wide 128-bit load is
-// contiguous; four decision bits per cell go to trace units of Q nibbles ([row][block][pair slot]).  One thread per
-// pair (G = 1): the two units of a row are written as one 16-byte record and two rows share a 32-byte sector
-// ([row / 2][pair slot][row % 2]), because the traceback reads a single pair's rows and pays per sector.
+// contiguous; four decision bits per cell go to trace units of Q cells, stored as four bit planes ([row][block][pair
+// slot]).  One thread per pair (G = 1): the two units of a row are written as one 16-byte record and two rows share a
+// 32-byte sector ([row / 2][pair slot][row % 2]), because the traceback reads a single pair's rows and pays per sector.
 #include "lara_gpu.cuh"
+
+#include <cstdlib>
 
 namespace lara
 {
@@ -51,26 +53,41 @@ namespace
 
 constexpr unsigned kFull = 0xffffffffu;
 
-// one trace unit = the Q decision nibbles of one run: 2, 4 or 8 bytes (Q = 12: 8 bytes, 12 nibbles used)
+// One trace unit = the decisions of one run of Q cells as four BIT PLANES of Q bits (plane k = decision bit k of
+// lara_gpu.cuh: kTrGap, kTrFromH, kTrVOpen, kTrHOpen; bit j of a plane = cell j of the run): 2, 4 or 8 bytes.
+//   Q = 16, 12: { P0 | P1 << 16, P2 | P3 << 16 }      Q = 8: P0 | P1 << 8 | P2 << 16 | P3 << 24      Q = 4: 4 bits each
+// The traceback tests ONE decision of a cell at a time (kernels_post.cu), which a plane answers with one shift; and a
+// plane grows by one funnel shift per cell with no chain between the four decisions of a cell.
 template <int Q>
-__device__ __forceinline__ void store_unit(void * base, size_t unitIdx, uint32_t const (&tw)[(Q + 7) / 8])
+__device__ __forceinline__ uint2 pack_unit(uint32_t const (&pl)[4])
 {
-    if constexpr (Q == 4) reinterpret_cast<uint16_t *>(base)[unitIdx] = (uint16_t)(tw[0] >> 16);
-    else if constexpr (Q == 8) reinterpret_cast<uint32_t *>(base)[unitIdx] = tw[0];
-    else if constexpr (Q == 12) reinterpret_cast<uint2 *>(base)[unitIdx] = make_uint2(tw[0], tw[1] >> 16);   // 12 of 16 nibbles
-    else reinterpret_cast<uint2 *>(base)[unitIdx] = make_uint2(tw[0], tw[1]);
+    if constexpr (Q == 4) return make_uint2(pl[0] | (pl[1] << 4) | (pl[2] << 8) | (pl[3] << 12), 0u);
+    else if constexpr (Q == 8) return make_uint2(pl[0] | (pl[1] << 8) | (pl[2] << 16) | (pl[3] << 24), 0u);
+    else return make_uint2(pl[0] | (pl[1] << 16), pl[2] | (pl[3] << 16));
+}
+template <int Q>
+__device__ __forceinline__ void store_unit(void * base, size_t unitIdx, uint32_t const (&pl)[4])
+{
+    uint2 const u = pack_unit<Q>(pl);
+    if constexpr (Q == 4) reinterpret_cast<uint16_t *>(base)[unitIdx] = (uint16_t)u.x;
+    else if constexpr (Q == 8) reinterpret_cast<uint32_t *>(base)[unitIdx] = u.x;
+    else reinterpret_cast<uint2 *>(base)[unitIdx] = u;
 }
 
 // One run of Q cells of row r on the diagonals of one block.  S[j], V[j]: latest cell of diagonal j (row r - 1 on
-// entry, row r on exit).  (hL, sL): H and S of the left neighbour of the run; (sU, vU): S and V of the upper
-// neighbour of the run's last cell.  Returns H of the run's last cell.  tw: Q decision nibbles, cell j in
-// word j / 8 at bits 4 (j % 8) (Q = 4: in the upper half word).
+// entry, row r on exit).  sub[j]: position specific score of cell j.  (hL, sL): H and S of the left
+// neighbour of the run; (sU, vU): S and V of the upper neighbour of the run's last cell.  Returns H of the run's last
+// cell.  pl: the four decision planes of the run, cell j at bit j.
+// Only H is carried along the run, IADD + VIMNMX per cell (see the header: the second operand of H is max(D, V) + go
+// of the cell before); the diagonal and vertical candidates come from row r - 1, and each of the four decisions goes
+// into its own plane with one funnel shift, so the cells of a run overlap freely in the instruction stream.
 // kLast: additionally captures S, V, H of cell jEnd (the end cell of the matrix, for SeqAn's _correctTraceValue).
 template <int Q, bool kLast>
 __device__ __forceinline__ int32_t band_run(int32_t (&S)[Q], int32_t (&V)[Q], int32_t const (&sub)[Q], int32_t hL, int32_t sL,
-                                            int32_t sU, int32_t vU, int32_t go, int32_t ge, uint32_t (&tw)[(Q + 7) / 8],
+                                            int32_t sU, int32_t vU, int32_t go, int32_t ge, uint32_t (&pl)[4],
                                             int jEnd, int32_t & sE, int32_t & vE, int32_t & hE)
 {
+    uint32_t p0 = 0u, p1 = 0u, p2 = 0u, p3 = 0u;
     int32_t h = hL, m = sL + go;
     #pragma unroll
     for (int j = 0; j < Q; ++j)
@@ -80,37 +97,38 @@ __device__ __forceinline__ int32_t band_run(int32_t (&S)[Q], int32_t (&V)[Q], in
         int32_t const dd = S[j] + sub[j];
         int32_t const ve = uv + ge, vo = us + go;
         int32_t const v = max(ve, vo);
+        p2 = __funnelshift_l((uint32_t)(ve - vo), p2, 1);               // V opened   (extension wins ties)
         int32_t const he = h + ge;
         int32_t const hn = max(he, m);
-        int32_t const gg = max(v, hn);
-        int32_t const s = max(dd, gg);
-        uint32_t n = (uint32_t)(he - m) >> 31;                          // bit 3: H opened   (extension wins ties)
-        n = __funnelshift_l((uint32_t)(ve - vo), n, 1);                 // bit 2: V opened   (extension wins ties)
-        n = __funnelshift_l((uint32_t)(v - hn), n, 1);                  // bit 1: gap from H (vertical wins ties)
-        n = __funnelshift_l((uint32_t)(dd - gg), n, 1);                 // bit 0: S from gap (diagonal wins ties)
-        tw[j >> 3] = __funnelshift_r(tw[j >> 3], n, 4);
-        m = max(dd, v) + go;
+        p3 = __funnelshift_l((uint32_t)(he - m), p3, 1);                // H opened   (extension wins ties)
+        int32_t const mx = max(dd, v);
+        int32_t const s = max(mx, hn);
+        p1 = __funnelshift_l((uint32_t)(v - hn), p1, 1);                // gap from H (vertical wins ties)
+        p0 = __funnelshift_l((uint32_t)(dd - s), p0, 1);                // S from gap (diagonal wins ties): gap > dd <=> s > dd
+        m = mx + go;                                                    // what the next cell's H opens from
         h = hn;
         S[j] = s;
         V[j] = v;
         if (kLast && j == jEnd) { sE = s; vE = v; hE = hn; }
     }
+    // the funnel shifts pushed cell j to bit Q - 1 - j
+    pl[0] = __brev(p0) >> (32 - Q); pl[1] = __brev(p1) >> (32 - Q); pl[2] = __brev(p2) >> (32 - Q); pl[3] = __brev(p3) >> (32 - Q);
     return h;
 }
 
+// The fill of the warp groups of ONE band shape: warp `warp` of the shape's part of the grid works on the slots
+// [warp * 32 / G, (warp + 1) * 32 / G) of pairIdx[0 .. nSlots).
 template <int G, int Q>
-__global__ void __launch_bounds__(128)
-gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc,
-                  PairState * __restrict__ state, int32_t * __restrict__ arena, int32_t go, int32_t ge)
+__device__ __forceinline__ void
+band_body(int const warp, int nSlots, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc,
+          PairState * __restrict__ state, int32_t * __restrict__ arena, int32_t go, int32_t ge)
 {
     constexpr int PPW = 32 / G;                                 // pairs per warp
     constexpr int W = 2 * G * Q;                                // diagonals of the band
     constexpr int NCH = W / 4;                                  // 16-byte value chunks per row
     constexpr int NU = 2 * G;                                   // trace units per row
     constexpr int CQ = Q / 4;                                   // value chunks per block
-    constexpr int TW = (Q + 7) / 8;
     constexpr int kPrefetchRows = 48 / Q;                       // L2 prefetch distance: about the same time for every Q
-    int const warp = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
     int const lane = threadIdx.x & 31;
     if (warp * PPW >= nSlots)
         return;
@@ -189,7 +207,7 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
     }
 
     int const nIter = lbMax + G;
-    uint32_t twA[2] = {0u, 0u};                                     // G == 1: block A's unit waits for block B's
+    uint2 unitA = make_uint2(0u, 0u);                               // G == 1: block A's unit waits for block B's
     for (int i = 0; i < nIter; ++i)
     {
         int const r = i - g + 1;
@@ -227,15 +245,13 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
             }
             if (rowValid)
             {
-                uint32_t tw[TW];
-                #pragma unroll
-                for (int k = 0; k < TW; ++k) tw[k] = 0u;
+                uint32_t pl[4];
                 if (r == lb && bEnd == 2 * g)
-                    HA = band_run<Q, true>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, tw, jEnd, sE, vE, hE);
+                    HA = band_run<Q, true>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, pl, jEnd, sE, vE, hE);
                 else
-                    HA = band_run<Q, false>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, tw, 0, sE, vE, hE);
-                if constexpr (G == 1) { twA[0] = tw[0]; twA[1] = tw[TW - 1]; }
-                else store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g)) * PPW + gs, tw);
+                    HA = band_run<Q, false>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, pl, 0, sE, vE, hE);
+                if constexpr (G == 1) unitA = pack_unit<Q>(pl);
+                else store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g)) * PPW + gs, pl);
             }
         }
         if constexpr (kDeep)
@@ -267,21 +283,19 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
             }
             if (rowValid)
             {
-                uint32_t tw[TW];
-                #pragma unroll
-                for (int k = 0; k < TW; ++k) tw[k] = 0u;
+                uint32_t pl[4];
                 if (r == lb && bEnd == 2 * g + 1)
-                    HB = band_run<Q, true>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, tw, jEnd, sE, vE, hE);
+                    HB = band_run<Q, true>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, pl, jEnd, sE, vE, hE);
                 else
-                    HB = band_run<Q, false>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, tw, 0, sE, vE, hE);
+                    HB = band_run<Q, false>(SB, VB, subB, HA, SA[Q - 1], sU, vU, go, ge, pl, 0, sE, vE, hE);
                 if constexpr (G == 1)
                 {
-                    static_assert(G != 1 || TW == 2, "one thread per pair: units of 8 bytes");
-                    uint4 const rec = (Q == 12) ? make_uint4(twA[0], twA[1] >> 16, tw[0], tw[TW - 1] >> 16)
-                                                : make_uint4(twA[0], twA[1], tw[0], tw[TW - 1]);
-                    reinterpret_cast<uint4 *>(trace)[(((size_t)(r >> 1) * PPW + gs) << 1) + (r & 1)] = rec;
+                    static_assert(G != 1 || Q >= 12, "one thread per pair: units of 8 bytes");
+                    uint2 const unitB = pack_unit<Q>(pl);
+                    reinterpret_cast<uint4 *>(trace)[(((size_t)(r >> 1) * PPW + gs) << 1) + (r & 1)] =
+                        make_uint4(unitA.x, unitA.y, unitB.x, unitB.y);
                 }
-                else store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g + 1)) * PPW + gs, tw);
+                else store_unit<Q>(trace, ((size_t)r * NU + (size_t)(2 * g + 1)) * PPW + gs, pl);
             }
         }
         if constexpr (kDeep)
@@ -297,83 +311,319 @@ gotoh_band_kernel(int nSlots, int32_t const * __restrict__ pairIdx, PairDesc con
     }
 }
 
-// Dense list of the slots whose pair is still iterating, in the old order (stable: the pairs of a warp group that
-// all go on stay neighbours, so the DP's loads stay coalesced).  One block; n is a batch's slot count.
-__global__ void __launch_bounds__(1024)
-compact_slots_kernel(int n, int32_t const * __restrict__ in, PairState const * __restrict__ state,
-                     int32_t * __restrict__ out, int32_t * __restrict__ count)
+// Two runs side by side in one instruction stream: block B of row r and block A of row r + 1 (one thread per pair).
+// They are independent but for one neighbour cell: the upper neighbour of A's last cell is B's first cell of row r,
+// which B produces first.  B's left neighbour (hLB, sLB) = last cell of A's row r, A's left neighbour (hLA, sLA) =
+// inflow from region L.  Two H chains and eight decision planes advance together, so a warp that has a scheduler
+// to itself (the usual case: one thread per pair leaves the machine with about one warp per scheduler) does not wait
+// for its own previous instruction.
+// The scores of the NEXT iteration (block B of row r + 1 from nextB, block A of row r + 2 from nextA; nullptr: none)
+// are loaded into subB / subA chunk by chunk as soon as this iteration has used a chunk: a whole iteration of lead
+// time without a second set of registers.
+// kLast: captures S, V, H of cell jEndB of block B or jEndA of block A (-1: none).
+template <int Q, bool kLast>
+__device__ __forceinline__ void band_run2(int32_t (&SB)[Q], int32_t (&VB)[Q], int32_t (&subB)[Q], int32_t hLB, int32_t sLB,
+                                          int32_t sUB, int32_t vUB, uint32_t (&plB)[4], int32_t & HB,
+                                          int32_t (&SA)[Q], int32_t (&VA)[Q], int32_t (&subA)[Q], int32_t hLA, int32_t sLA,
+                                          uint32_t (&plA)[4], int32_t & HA, int32_t go, int32_t ge,
+                                          int4 const * __restrict__ nextB, int4 const * __restrict__ nextA,
+                                          int jEndB, int jEndA, int32_t & sE, int32_t & vE, int32_t & hE)
 {
-    __shared__ int warpCount[32];
-    __shared__ int base;
-    int const tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    if (tid == 0) base = 0;
-    __syncthreads();
-    for (int i0 = 0; i0 < n; i0 += 1024)
+    uint32_t b0 = 0u, b1 = 0u, b2 = 0u, b3 = 0u, a0 = 0u, a1 = 0u, a2 = 0u, a3 = 0u;
+    int32_t hB = hLB, mB = sLB + go, hA = hLA, mA = sLA + go;
+    #pragma unroll
+    for (int j = 0; j < Q; ++j)
     {
-        int const i = i0 + tid;
-        int const p = i < n ? in[i] : -1;
-        bool const live = p >= 0 && state[p].done == 0;
-        unsigned const bal = __ballot_sync(kFull, live);
-        if (lane == 0) warpCount[w] = __popc(bal);
-        __syncthreads();
-        int before = 0, total = 0;
-        #pragma unroll
-        for (int k = 0; k < 32; ++k)
         {
-            int const c = warpCount[k];
-            before += k < w ? c : 0;
-            total += c;
+            int32_t const us = (j + 1 < Q) ? SB[j + 1] : sUB;
+            int32_t const uv = (j + 1 < Q) ? VB[j + 1] : vUB;
+            int32_t const dd = SB[j] + subB[j];
+            int32_t const ve = uv + ge, vo = us + go;
+            int32_t const v = max(ve, vo);
+            b2 = __funnelshift_l((uint32_t)(ve - vo), b2, 1);
+            int32_t const he = hB + ge;
+            int32_t const hn = max(he, mB);
+            b3 = __funnelshift_l((uint32_t)(he - mB), b3, 1);
+            int32_t const mx = max(dd, v);
+            int32_t const s = max(mx, hn);
+            b1 = __funnelshift_l((uint32_t)(v - hn), b1, 1);
+            b0 = __funnelshift_l((uint32_t)(dd - s), b0, 1);
+            mB = mx + go;
+            hB = hn;
+            SB[j] = s;
+            VB[j] = v;
+            if (kLast && j == jEndB) { sE = s; vE = v; hE = hn; }
         }
-        int const b = base;
-        if (live) out[b + before + __popc(bal & ((1u << lane) - 1u))] = p;
-        __syncthreads();
-        if (tid == 0) base = b + total;
-        __syncthreads();
+        {
+            // the upper neighbour of A's last cell: B's first cell of this row, written above at j = 0
+            int32_t const us = (j + 1 < Q) ? SA[j + 1] : SB[0];
+            int32_t const uv = (j + 1 < Q) ? VA[j + 1] : VB[0];
+            int32_t const dd = SA[j] + subA[j];
+            int32_t const ve = uv + ge, vo = us + go;
+            int32_t const v = max(ve, vo);
+            a2 = __funnelshift_l((uint32_t)(ve - vo), a2, 1);
+            int32_t const he = hA + ge;
+            int32_t const hn = max(he, mA);
+            a3 = __funnelshift_l((uint32_t)(he - mA), a3, 1);
+            int32_t const mx = max(dd, v);
+            int32_t const s = max(mx, hn);
+            a1 = __funnelshift_l((uint32_t)(v - hn), a1, 1);
+            a0 = __funnelshift_l((uint32_t)(dd - s), a0, 1);
+            mA = mx + go;
+            hA = hn;
+            SA[j] = s;
+            VA[j] = v;
+            if (kLast && j == jEndA) { sE = s; vE = v; hE = hn; }
+        }
+        if ((j & 3) == 3)
+        {
+            // this chunk of scores has been used: fetch the next iteration's into the same registers
+            int const k = j >> 2;
+            if (nextB != nullptr)
+            {
+                int4 const x = __ldg(nextB + (size_t)k * 32);
+                subB[4 * k] = x.x; subB[4 * k + 1] = x.y; subB[4 * k + 2] = x.z; subB[4 * k + 3] = x.w;
+            }
+            if (nextA != nullptr)
+            {
+                int4 const x = __ldg(nextA + (size_t)k * 32);
+                subA[4 * k] = x.x; subA[4 * k + 1] = x.y; subA[4 * k + 2] = x.z; subA[4 * k + 3] = x.w;
+            }
+        }
     }
-    if (tid == 0) *count = base;
+    plB[0] = __brev(b0) >> (32 - Q); plB[1] = __brev(b1) >> (32 - Q); plB[2] = __brev(b2) >> (32 - Q); plB[3] = __brev(b3) >> (32 - Q);
+    plA[0] = __brev(a0) >> (32 - Q); plA[1] = __brev(a1) >> (32 - Q); plA[2] = __brev(a2) >> (32 - Q); plA[3] = __brev(a3) >> (32 - Q);
+    HB = hB;
+    HA = hA;
 }
 
-template <int G, int Q>
-cudaError_t launch_gq(int nSlots, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
-                      int32_t go, int32_t ge, cudaStream_t stream)
+// One thread per pair (G = 1, band of 2 Q diagonals): the same fill as band_body<1, Q>, with the loop turned by half
+// a row: an iteration computes block B of row r together with block A of row r + 1 (band_run2).  In the iteration of
+// the pair's last row the A half works on nothing (its results are not used).
+template <int Q>
+__device__ __forceinline__ void
+band_body_one(int const warp, int nSlots, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc,
+              PairState * __restrict__ state, int32_t * __restrict__ arena, int32_t go, int32_t ge)
 {
-    int const slotsPerBlock = 4 * (32 / G);
-    int const blocks = (nSlots + slotsPerBlock - 1) / slotsPerBlock;
-    gotoh_band_kernel<G, Q><<<blocks, 128, 0, stream>>>(nSlots, pairIdx, desc, state, arena, go, ge);
-    return cudaGetLastError();
+    constexpr int PPW = 32;
+    constexpr int W = 2 * Q;
+    constexpr int NCH = W / 4;
+    constexpr int CQ = Q / 4;
+    constexpr int kPrefetchRows = 48 / Q + 1;
+    int const lane = threadIdx.x & 31;
+    if (warp * PPW >= nSlots)
+        return;
+    int const slot = warp * PPW + lane;
+    int p = slot < nSlots ? pairIdx[slot] : -1;
+    if (p >= 0 && state[p].done)
+        p = -1;
+    bool const live = p >= 0;
+    PairDesc const & d = desc[live ? p : 0];
+    int const la = live ? d.la : -1, lb = live ? d.lb : -1;
+    int const dLo = live ? d.dLo : 0;
+    int lbMax = lb;
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lbMax = max(lbMax, __shfl_xor_sync(kFull, lbMax, o));
+    if (lbMax < 1)
+        return;
+    int const gs = live ? d.bandSlot : 0;
+    int4 const * __restrict__ vals = reinterpret_cast<int4 const *>(arena + d.offBVals) + gs;
+    uint4 * const trace = reinterpret_cast<uint4 *>(arena + d.offBTrace);
+    int4 * __restrict__ uRec = reinterpret_cast<int4 *>(arena + d.offU) + gs;
+    int4 * __restrict__ lRec = reinterpret_cast<int4 *>(arena + d.offL) + gs;
+    int const idxEnd = la - lb - dLo;
+    int const bEnd = (live && idxEnd >= 0 && idxEnd < W) ? idxEnd / Q : -1;
+    int const jEnd = idxEnd - bEnd * Q;
+
+    // row 0
+    int32_t SA[Q], VA[Q], SB[Q], VB[Q];
+    #pragma unroll
+    for (int j = 0; j < Q; ++j)
+    {
+        int const ca = dLo + j, cb = dLo + Q + j;
+        SA[j] = ca > 0 ? go + (ca - 1) * ge : (ca == 0 ? 0 : kBandNeg);
+        SB[j] = cb > 0 ? go + (cb - 1) * ge : (cb == 0 ? 0 : kBandNeg);
+        VA[j] = kBandNeg;
+        VB[j] = kBandNeg;
+    }
+    int32_t HA = (dLo + Q - 1 > 0) ? SA[Q - 1] : kBandNeg;
+    int32_t HB = (dLo + 2 * Q - 1 > 0) ? SB[Q - 1] : kBandNeg;
+    int32_t runU = kDpNeg, runL = kDpNeg;
+    int32_t sE = 0, vE = 0, hE = 0;
+
+    auto run_ptr = [&](int row, int block) -> int4 const *
+    {
+        return (row >= 1 && row <= lb) ? vals + ((size_t)row * NCH + (size_t)block * CQ) * PPW : nullptr;
+    };
+    auto load_run = [&](int32_t (&sub)[Q], int row, int block)
+    {
+        int4 const * __restrict__ src = run_ptr(row, block);
+        if (src == nullptr) return;
+        #pragma unroll
+        for (int k = 0; k < CQ; ++k)
+        {
+            int4 const x = __ldg(src + (size_t)k * PPW);
+            sub[4 * k] = x.x; sub[4 * k + 1] = x.y; sub[4 * k + 2] = x.z; sub[4 * k + 3] = x.w;
+        }
+    };
+    // inflow from region L into block A of row r (left neighbour of its first cell), record of column c - 1
+    auto inflow_l = [&](int r, int32_t & hL, int32_t & sL)
+    {
+        int const c = r + dLo;
+        hL = kBandNeg; sL = kBandNeg;
+        if (r >= 1 && r <= lb && c >= 1 && c - 1 <= la)
+        {
+            int32_t const tv = VA[0] + ge, ts = SA[0] + go;
+            int32_t const vl = max(tv, ts);
+            hL = (c - 1 >= 1) ? (c + r - 2) * ge + go + runL : kBandNeg;
+            sL = max(vl, hL);
+            lRec[(size_t)(c - 1) * PPW] = make_int4(tv - r * ge, ts - r * ge, runL, 0);
+            runL = max(runL, vl - r * ge - (c - 1) * ge);
+        }
+    };
+    // inflow from region U into block B of row r (upper neighbour of its last cell), record of row r - 1
+    auto inflow_u = [&](int r, int32_t & sU, int32_t & vU)
+    {
+        int const c = r + dLo + W - 1;
+        sU = kBandNeg; vU = kBandNeg;
+        if (live && r >= 1 && r - 1 <= lb && c - 1 <= la)
+        {
+            int32_t const th = HB + ge, ts = SB[Q - 1] + go;
+            int32_t const hu = max(th, ts);
+            vU = (r - 1 >= 1) ? (c + r - 2) * ge + go + runU : kBandNeg;
+            sU = max(vU, hu);
+            uRec[(size_t)(r - 1) * PPW] = make_int4(th - c * ge, ts - c * ge, runU, 0);
+            runU = max(runU, hu - c * ge - (r - 1) * ge);
+        }
+    };
+
+    int32_t subA[Q], subB[Q];
+    #pragma unroll
+    for (int j = 0; j < Q; ++j) { subA[j] = kDpNeg; subB[j] = kDpNeg; }
+    load_run(subA, 1, 0);
+    load_run(subB, 1, 1);
+    // ---- block A of row 1 -------------------------------------------------------------------------------------------
+    uint2 unitA = make_uint2(0u, 0u);
+    {
+        int32_t hL, sL;
+        inflow_l(1, hL, sL);
+        if (lb >= 1)
+        {
+            uint32_t pl[4];
+            HA = band_run<Q, true>(SA, VA, subA, hL, sL, SB[0], VB[0], go, ge, pl, (lb == 1 && bEnd == 0) ? jEnd : -1, sE, vE, hE);
+            unitA = pack_unit<Q>(pl);
+        }
+    }
+    load_run(subA, 2, 0);
+    // ---- iteration r: block B of row r and block A of row r + 1; row lb + 1 only closes region U's record of row lb --
+    for (int r = 1; r <= lbMax + 1; ++r)
+    {
+        if (r + kPrefetchRows <= lb)
+        {
+            int4 const * __restrict__ src = vals + (size_t)(r + kPrefetchRows) * NCH * PPW;
+            #pragma unroll
+            for (int k = 0; k < 2 * CQ; ++k)
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(src + (size_t)k * PPW));
+        }
+        int32_t sU, vU, hL, sL;
+        inflow_u(r, sU, vU);                     // from row r - 1 of diagonal dHi
+        if (r > lb) continue;
+        inflow_l(r + 1, hL, sL);                 // from row r of diagonal dLo
+        uint32_t plB[4], plA[4];
+        int4 const * const nB = run_ptr(r + 1, 1), * const nA = run_ptr(r + 2, 0);
+        if (r + 1 < lb)
+            band_run2<Q, false>(SB, VB, subB, HA, SA[Q - 1], sU, vU, plB, HB, SA, VA, subA, hL, sL, plA, HA, go, ge, nB, nA, -1, -1, sE, vE, hE);
+        else
+            band_run2<Q, true>(SB, VB, subB, HA, SA[Q - 1], sU, vU, plB, HB, SA, VA, subA, hL, sL, plA, HA, go, ge, nB, nA,
+                               (r == lb && bEnd == 1) ? jEnd : -1, (r + 1 == lb && bEnd == 0) ? jEnd : -1, sE, vE, hE);
+        uint2 const unitB = pack_unit<Q>(plB);
+        trace[(((size_t)(r >> 1) * PPW + gs) << 1) + (r & 1)] = make_uint4(unitA.x, unitA.y, unitB.x, unitB.y);
+        unitA = pack_unit<Q>(plA);
+    }
+    if (bEnd >= 0)
+    {
+        PairState & st = state[p];
+        st.currentUpper = sE; st.sEnd = sE; st.vEnd = vE; st.hEnd = hE;
+    }
+}
+
+// One launch per iteration for ALL band shapes of a batch: the grid is the concatenation of the shapes' parts (the
+// shape with the most slots first), a block looks up its part in the class table and runs that shape's body.  Separate
+// launches per shape had to run side by side on streams (fork / join events every iteration), and a shape with a
+// handful of pairs then set the latency of the whole iteration step.
+#define LARA_BAND_SHAPES(X) \
+    X(1, 16) X(2, 16) X(4, 16) X(8, 16) X(16, 16) X(32, 16) \
+    X(1, 12) \
+    X(2, 8) X(4, 8) X(8, 8) X(16, 8) X(32, 8) \
+    X(4, 4) X(8, 4) X(16, 4) X(32, 4)
+
+// kOne: the launch has one-thread-per-pair classes in their two-rows-at-a-time form (more registers per thread; a
+// launch without such classes runs the instantiation without them and keeps its occupancy).
+template <bool kOne>
+__global__ void __launch_bounds__(128)
+gotoh_band_kernel(BandClassTable const tab, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc,
+                  PairState * __restrict__ state, int32_t * __restrict__ arena, int32_t go, int32_t ge)
+{
+    int c = 0;
+    while (c + 1 < tab.n && (int)blockIdx.x >= tab.firstBlock[c + 1]) ++c;
+    int const warp = ((int)blockIdx.x - tab.firstBlock[c]) * 4 + (int)(threadIdx.x >> 5);
+    int32_t const * __restrict__ slots = pairIdx + tab.slotOffset[c];
+    int const nSlots = tab.nSlots[c];
+    switch (tab.shape[c])
+    {
+        // one thread per pair: the form that works on two rows at a time
+        case (0x10000 | (1 << 8) | 16): if constexpr (kOne) band_body_one<16>(warp, nSlots, slots, desc, state, arena, go, ge); break;
+        case (0x10000 | (1 << 8) | 12): if constexpr (kOne) band_body_one<12>(warp, nSlots, slots, desc, state, arena, go, ge); break;
+#define LARA_CASE(g_, q_) case ((g_) << 8) | (q_): band_body<g_, q_>(warp, nSlots, slots, desc, state, arena, go, ge); break;
+        LARA_BAND_SHAPES(LARA_CASE)
+#undef LARA_CASE
+        default: break;
+    }
 }
 
 } // namespace
 
-cudaError_t launch_compact_slots(int n, int32_t const * in, PairState const * state, int32_t * out, int32_t * count,
-                                 cudaStream_t stream)
-{
-    if (n <= 0) return cudaSuccess;
-    compact_slots_kernel<<<1, 1024, 0, stream>>>(n, in, state, out, count);
-    return cudaGetLastError();
-}
-
 bool band_shape_supported(int G, int Q)
 {
-    if (Q == 16) return G == 1 || G == 2 || G == 4 || G == 8 || G == 16 || G == 32;
-    if (Q == 12) return G == 1;
-    if (Q == 8) return G == 2 || G == 4 || G == 8 || G == 16 || G == 32;
-    if (Q == 4) return G == 4 || G == 8 || G == 16 || G == 32;
+#define LARA_CASE(g_, q_) if (G == g_ && Q == q_) return true;
+    LARA_BAND_SHAPES(LARA_CASE)
+#undef LARA_CASE
     return false;
+}
+
+cudaError_t launch_gotoh_band_multi(int nClasses, BandLaunch const * cls, int32_t const * pairIdx, PairDesc const * desc,
+                                    PairState * state, int32_t * arena, int32_t go, int32_t ge, cudaStream_t stream)
+{
+    BandClassTable tab{};
+    int blocks = 0;
+    bool anyOne = false;
+    for (int k = 0; k < nClasses; ++k)
+    {
+        if (cls[k].nSlots <= 0) continue;
+        if (tab.n >= kMaxBandClasses || !band_shape_supported(cls[k].G, cls[k].Q)) return cudaErrorInvalidValue;
+        int const slotsPerBlock = 4 * (32 / cls[k].G);
+        // LARA_B200_FUSED=0: the one-thread-per-pair shapes run the generic body (measurement switch, same results)
+        static bool const fused = []() { char const * e = std::getenv("LARA_B200_FUSED"); return !e || std::atoi(e) != 0; }();
+        tab.shape[tab.n] = (cls[k].G << 8) | cls[k].Q | ((fused && cls[k].G == 1) ? 0x10000 : 0);
+        anyOne = anyOne || (fused && cls[k].G == 1);
+        tab.firstBlock[tab.n] = blocks;
+        tab.slotOffset[tab.n] = cls[k].slotOffset;
+        tab.nSlots[tab.n] = cls[k].nSlots;
+        blocks += (cls[k].nSlots + slotsPerBlock - 1) / slotsPerBlock;
+        ++tab.n;
+    }
+    if (blocks == 0) return cudaSuccess;
+    tab.firstBlock[tab.n] = blocks;
+    if (anyOne) gotoh_band_kernel<true><<<blocks, 128, 0, stream>>>(tab, pairIdx, desc, state, arena, go, ge);
+    else gotoh_band_kernel<false><<<blocks, 128, 0, stream>>>(tab, pairIdx, desc, state, arena, go, ge);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_gotoh_band(int G, int Q, int nSlots, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t go, int32_t ge, cudaStream_t stream)
 {
-    if (nSlots <= 0)
-        return cudaSuccess;
-#define LARA_GQ(g_, q_) if (G == g_ && Q == q_) return launch_gq<g_, q_>(nSlots, pairIdx, desc, state, arena, go, ge, stream);
-    LARA_GQ(1, 16) LARA_GQ(2, 16) LARA_GQ(4, 16) LARA_GQ(8, 16) LARA_GQ(16, 16) LARA_GQ(32, 16)
-    LARA_GQ(1, 12)
-    LARA_GQ(2, 8) LARA_GQ(4, 8) LARA_GQ(8, 8) LARA_GQ(16, 8) LARA_GQ(32, 8)
-    LARA_GQ(4, 4) LARA_GQ(8, 4) LARA_GQ(16, 4) LARA_GQ(32, 4)
-#undef LARA_GQ
-    return cudaErrorInvalidValue;
+    BandLaunch one{G, Q, nSlots, 0};
+    return launch_gotoh_band_multi(1, &one, pairIdx, desc, state, arena, go, ge, stream);
 }
 
 } // namespace lara

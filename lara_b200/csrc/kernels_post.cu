@@ -318,9 +318,9 @@ __device__ void band_end_values(BandView const & v, int32_t & sE, int32_t & vE, 
 }
 
 // Traceback + evaluateLines for band mode: the segment walker of traceback_walk over a polymorphic cell fetch.
-// Window = 32 rows x 32 band diagonals around the walker, in shared memory: lane i fetches row rHi - i as eight
-// half words (4 nibbles each) and packs them into win[4 i .. 4 i + 3], nibble x of the window at bits 4 (x % 8)
-// of word x / 8.
+// Window = 32 rows x 32 band diagonals around the walker, in shared memory as four decision planes per row: lane i
+// fetches row rHi - i (the trace units of kernels_band.cu are bit planes already) and writes win[4 i + k] = plane k of
+// that row, window diagonal x at bit x.  The walk asks for one decision of a cell at a time.
 __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, int32_t hEnd, uint32_t * linesRev,
                               uint32_t * win, int32_t & gapOut, int lane)
 {
@@ -348,44 +348,63 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             uint32_t w[4] = {0u, 0u, 0u, 0u};
             if (rr >= 1)
             {
-                if (v.ppw == 32)
+                if (v.ppw == 32 || v.Q == 16)
                 {
-                    // one thread per pair (Q = 16 or 12): 16-byte row records, two rows per sector
-                    uint4 const u = __ldg(reinterpret_cast<uint4 const *>(v.trace) + ((((size_t)(rr >> 1) * 32 + v.slot) << 1) + (rr & 1)));
-                    if (v.Q == 16) { w[0] = u.x; w[1] = u.y; w[2] = u.z; w[3] = u.w; }
-                    else { w[0] = u.x; w[1] = (u.y & 0xffffu) | (u.z << 16); w[2] = (u.z >> 16) | (u.w << 16); w[3] = 0u; }
-                }
-                else if (v.Q == 16)
-                {
-                    // units of 16 nibbles (8 bytes); xLo is a multiple of 16
-                    uint2 const * __restrict__ src = reinterpret_cast<uint2 const *>(v.trace) +
-                                                     ((size_t)rr * nUnits + (xLo >> 4)) * v.ppw + v.slot;
-                    uint2 const u0 = __ldg(src), u1 = __ldg(src + v.ppw);
-                    w[0] = u0.x; w[1] = u0.y; w[2] = u1.x; w[3] = u1.y;
+                    // units of 8 bytes { P0 | P1 << 16, P2 | P3 << 16 }; one thread per pair (Q = 16 or 12): both units of
+                    // a row in one 16-byte record, two rows per sector; else two neighbouring units (xLo is a multiple of 16)
+                    uint4 u;
+                    if (v.ppw == 32)
+                        u = __ldg(reinterpret_cast<uint4 const *>(v.trace) + ((((size_t)(rr >> 1) * 32 + v.slot) << 1) + (rr & 1)));
+                    else
+                    {
+                        uint2 const * __restrict__ src = reinterpret_cast<uint2 const *>(v.trace) +
+                                                         ((size_t)rr * nUnits + (xLo >> 4)) * v.ppw + v.slot;
+                        uint2 const u0 = __ldg(src), u1 = __ldg(src + v.ppw);
+                        u = make_uint4(u0.x, u0.y, u1.x, u1.y);
+                    }
+                    if (v.Q == 16)
+                    {
+                        w[0] = __byte_perm(u.x, u.z, 0x5410); w[1] = __byte_perm(u.x, u.z, 0x7632);
+                        w[2] = __byte_perm(u.y, u.w, 0x5410); w[3] = __byte_perm(u.y, u.w, 0x7632);
+                    }
+                    else
+                    {
+                        // 12-bit planes: block B's continue at bit 12
+                        w[0] = (u.x & 0xfffu) | ((u.z & 0xfffu) << 12); w[1] = ((u.x >> 16) & 0xfffu) | (((u.z >> 16) & 0xfffu) << 12);
+                        w[2] = (u.y & 0xfffu) | ((u.w & 0xfffu) << 12); w[3] = ((u.y >> 16) & 0xfffu) | (((u.w >> 16) & 0xfffu) << 12);
+                    }
                 }
                 else if (v.Q == 8)
                 {
-                    // units of 8 nibbles (one word)
+                    // units of one word P0 | P1 << 8 | P2 << 16 | P3 << 24: plane k of the window = byte k of four units
                     uint32_t const * __restrict__ src = reinterpret_cast<uint32_t const *>(v.trace) +
                                                         ((size_t)rr * nUnits + (xLo >> 3)) * v.ppw + v.slot;
-                    #pragma unroll
-                    for (int h = 0; h < 4; ++h) w[h] = __ldg(src + (size_t)h * v.ppw);
+                    uint32_t const a0 = __ldg(src), a1 = __ldg(src + v.ppw), a2 = __ldg(src + 2 * (size_t)v.ppw), a3 = __ldg(src + 3 * (size_t)v.ppw);
+                    uint32_t const lo01 = __byte_perm(a0, a1, 0x5140), hi01 = __byte_perm(a0, a1, 0x7362);   // { a0.b0, a1.b0, a0.b1, a1.b1 }, { b2, b2, b3, b3 }
+                    uint32_t const lo23 = __byte_perm(a2, a3, 0x5140), hi23 = __byte_perm(a2, a3, 0x7362);
+                    w[0] = __byte_perm(lo01, lo23, 0x5410); w[1] = __byte_perm(lo01, lo23, 0x7632);
+                    w[2] = __byte_perm(hi01, hi23, 0x5410); w[3] = __byte_perm(hi01, hi23, 0x7632);
                 }
                 else
                 {
-                    // units of 4 nibbles (one half word)
+                    // units of one half word P0 | P1 << 4 | P2 << 8 | P3 << 12: plane k of the window = nibble k of eight units
                     uint16_t const * __restrict__ src = v.trace + ((size_t)rr * nUnits + (xLo >> 2)) * v.ppw + v.slot;
                     #pragma unroll
                     for (int h = 0; h < 8; ++h)
-                        w[h >> 1] |= (uint32_t)__ldg(src + (size_t)h * v.ppw) << (16 * (h & 1));
+                    {
+                        uint32_t const u = (uint32_t)__ldg(src + (size_t)h * v.ppw);
+                        #pragma unroll
+                        for (int k = 0; k < 4; ++k) w[k] |= ((u >> (4 * k)) & 15u) << (4 * h);
+                    }
                 }
             }
             *reinterpret_cast<uint4 *>(win + 4 * lane) = make_uint4(w[0], w[1], w[2], w[3]);
         }
         __syncwarp();
-        // known(ci, ri): the trace decision of that cell can be evaluated now
-        // outside: the cell lies in a closed-form region and was not evaluated (lazy == true)
-        auto fetch = [&](int ci, int ri, bool & known, bool & outside, bool lazy) -> uint32_t
+        // One decision (bit `plane` of the trace nibble) of cell (ci, ri).
+        // known: the decision can be evaluated now; outside: the cell lies in a closed-form region and was not
+        // evaluated (lazy == true)
+        auto fetch = [&](int ci, int ri, int plane, bool & known, bool & outside, bool lazy) -> uint32_t
         {
             known = false; outside = false;
             if (ci < 1 || ri < 1) return 0u;
@@ -394,12 +413,12 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             {
                 if (lazy) { outside = true; return 0u; }
                 known = true;
-                return band_outside_nib(v, ci, ri);
+                return (band_outside_nib(v, ci, ri) >> plane) & 1u;
             }
             int const x = dd - v.dLo - xLo, row = rHi - ri;
             if (row > 31 || x < 0 || x > 31) return 0u;
             known = true;
-            return (win[4 * row + (x >> 3)] >> (4 * (x & 7))) & 15u;
+            return (win[4 * row + plane] >> x) & 1u;
         };
         for (;;)
         {
@@ -411,38 +430,38 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             if (state == 0)
             {
                 bool known, outside;
-                uint32_t nib = fetch(c - lane, r - lane, known, outside, false);   // one diagonal: all in or all out
-                if (first && lane == 0)
-                {
-                    if (endFix == 1) nib = (nib | kTrGap) & ~kTrFromH;
-                    else if (endFix == 2) nib = nib | kTrGap | kTrFromH;
-                }
-                first = false;
-                unsigned const diagMask = __ballot_sync(kFull, known && !(nib & kTrGap));
+                uint32_t isGap = fetch(c - lane, r - lane, 0, known, outside, false);   // one diagonal: all in or all out
+                if (first && lane == 0 && endFix != 0) isGap = 1u;
+                unsigned const diagMask = __ballot_sync(kFull, known && !isGap);
                 int const run = (diagMask == kFull) ? 32 : (__ffs(~diagMask) - 1);
                 if (run > 0)
                 {
                     if (lane < run)
                         linesRev[n + lane] = ((uint32_t)(c - lane - 1) << 16) | (uint32_t)(r - lane - 1);
                     n += run; c -= run; r -= run; prev = 0;
+                    first = false;
                     continue;
                 }
-                uint32_t const nib0 = __shfl_sync(kFull, nib, 0);
-                state = (nib0 & kTrFromH) ? 2 : 1;
+                // the walker's own cell took a gap: from the horizontal or the vertical matrix?
+                bool k2, o2;
+                uint32_t fromH = fetch(c, r, 1, k2, o2, false);
+                if (first) { if (endFix == 1) fromH = 0u; else if (endFix == 2) fromH = 1u; }
+                first = false;
+                state = fromH ? 2 : 1;
             }
             if (state == 1)
             {
                 // closed-form cells (beyond the band) are only evaluated when the run reaches them
                 bool known, outside;
-                uint32_t nib = fetch(c, r - lane, known, outside, true);
+                uint32_t opened = fetch(c, r - lane, 2, known, outside, true);
                 unsigned knownMask = __ballot_sync(kFull, known);
-                unsigned extMask = __ballot_sync(kFull, known && !(nib & kTrVOpen) && (r - lane) != 1);
+                unsigned extMask = __ballot_sync(kFull, known && !opened && (r - lane) != 1);
                 int m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
                 if (m < 32 && ((__ballot_sync(kFull, outside) >> m) & 1u))
                 {
-                    if (outside) { nib = band_outside_nib(v, c, r - lane); known = true; }
+                    if (outside) { opened = (band_outside_nib(v, c, r - lane) >> 2) & 1u; known = true; }
                     knownMask = __ballot_sync(kFull, known);
-                    extMask = __ballot_sync(kFull, known && !(nib & kTrVOpen) && (r - lane) != 1);
+                    extMask = __ballot_sync(kFull, known && !opened && (r - lane) != 1);
                     m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
                 }
                 bool const closes = m < 32 && ((knownMask >> m) & 1u);
@@ -459,15 +478,15 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             else
             {
                 bool known, outside;
-                uint32_t nib = fetch(c - lane, r, known, outside, true);
+                uint32_t opened = fetch(c - lane, r, 3, known, outside, true);
                 unsigned knownMask = __ballot_sync(kFull, known);
-                unsigned extMask = __ballot_sync(kFull, known && !(nib & kTrHOpen) && (c - lane) != 1);
+                unsigned extMask = __ballot_sync(kFull, known && !opened && (c - lane) != 1);
                 int m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
                 if (m < 32 && ((__ballot_sync(kFull, outside) >> m) & 1u))
                 {
-                    if (outside) { nib = band_outside_nib(v, c - lane, r); known = true; }
+                    if (outside) { opened = (band_outside_nib(v, c - lane, r) >> 3) & 1u; known = true; }
                     knownMask = __ballot_sync(kFull, known);
-                    extMask = __ballot_sync(kFull, known && !(nib & kTrHOpen) && (c - lane) != 1);
+                    extMask = __ballot_sync(kFull, known && !opened && (c - lane) != 1);
                     m = (extMask == kFull) ? 32 : (__ffs(~extMask) - 1);
                 }
                 bool const closes = m < 32 && ((knownMask >> m) & 1u);
@@ -648,7 +667,7 @@ __device__ __forceinline__ void
 iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
                   int32_t * __restrict__ arena, DevParams const & P, PairOutHdr * __restrict__ outHdr,
                   int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
-                  int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand, int tune, DevInputs const & in)
+                  int32_t * __restrict__ finishedList, int maxLa, int maxLb, int smemCand, int tune, DevInputs const & in)
 {
     extern __shared__ __align__(16) unsigned char smemRaw[];
     int const warpInBlock = threadIdx.x >> 5;
@@ -1088,7 +1107,9 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         div = __fdiv_rn(__fmul_rn(1.f, __uint2float_rn(P.libMax - P.libMin)), __int2float_rn(maxScore - minScore));
     }
     bool const swapIdx = d.seqFirst > d.seqSecond;
-    int32_t * __restrict__ out = outLines + outOff[p];
+    // the pair's result slot: its position in the device's prepared pair list (the batch arrays are in admission order)
+    int const oi = d.outIdx;
+    int32_t * __restrict__ out = outLines + outOff[oi];
     for (int i = lane; i < nBest; i += 32)
     {
         uint32_t const v = (uint32_t)arena[d.offBest + i];
@@ -1113,41 +1134,31 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         PairOutHdr h;
         h.bestLower = st.bestLower; h.bestUpper = st.bestUpper;
         h.iterations = P.numIterations - st.remaining; h.nLines = nBest;
-        outHdr[p] = h;
+        outHdr[oi] = h;
         st.done = 1;
-        atomicSub(activeCount, 1);
+        // tell the host: finished[0] counts, finished[1 ..] lists the finished pairs (its slot can take the next pair)
+        __threadfence();
+        int const at = atomicAdd(finishedList, 1);
+        finishedList[1 + at] = p;
     }
 }
 
-// Two launch forms.  workCounter == nullptr: warp w of the grid takes pair w.  Otherwise the grid is a fixed number of
-// one-warp blocks per SM (all of them resident from the start, so that a DP launch of another worker queued behind this
-// one is placed at once instead of waiting for the last wave of this grid) and every warp pulls pairs from the counter.
-template <bool kTracebackOnly, bool kPersistent>
-__global__ void __launch_bounds__(kPersistent ? 32 : 128, kPersistent ? 20 : 6)
-iterate_post_kernel(int n, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
+// Warp w of the grid takes slot w of the batch's slot table (pairIdx; nullptr: pair w); empty slots and pairs that
+// have finished return at once.
+template <bool kTracebackOnly>
+__global__ void __launch_bounds__(128, 6)
+iterate_post_kernel(int n, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
                     int32_t * __restrict__ arena, DevParams P, PairOutHdr * __restrict__ outHdr,
                     int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
-                    int32_t * __restrict__ activeCount, int maxLa, int maxLb, int smemCand, int tune, DevInputs in,
-                    int32_t * __restrict__ workCounter)
+                    int32_t * __restrict__ finished, int maxLa, int maxLb, int smemCand, int tune, DevInputs in)
 {
-    if (!kPersistent)
-    {
-        int const p = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
-        if (p < n)
-            iterate_post_pair<kTracebackOnly>(p, desc, state, arena, P, outHdr, outLines, outOff, activeCount, maxLa, maxLb,
-                                              smemCand, tune, in);
+    int const w = (int)((blockIdx.x * (unsigned)blockDim.x + threadIdx.x) >> 5);
+    if (w >= n)
         return;
-    }
-    for (;;)
-    {
-        __syncwarp();
-        int p = 0;
-        if ((threadIdx.x & 31) == 0) p = atomicAdd(workCounter, 1);
-        p = __shfl_sync(kFull, p, 0);
-        if (p >= n) break;
-        iterate_post_pair<kTracebackOnly>(p, desc, state, arena, P, outHdr, outLines, outOff, activeCount, maxLa, maxLb,
-                                          smemCand, tune, in);
-    }
+    int const p = pairIdx ? pairIdx[w] : w;
+    if (p < 0)
+        return;
+    iterate_post_pair<kTracebackOnly>(p, desc, state, arena, P, outHdr, outLines, outOff, finished, maxLa, maxLb, smemCand, tune, in);
 }
 
 size_t post_smem_per_warp(int maxLa, int maxLb, int smemCand)
@@ -1168,17 +1179,15 @@ cudaError_t post_configure_device()
     if (e != cudaSuccess) return e;
     e = cudaDeviceGetAttribute(&maxOptin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(iterate_post_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
+    e = cudaFuncSetAttribute(iterate_post_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(iterate_post_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(iterate_post_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
+    return cudaFuncSetAttribute(iterate_post_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, maxOptin);
 }
 
-cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
+cudaError_t launch_iterate_post(int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
                                 DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
-                                int32_t * activeCount, int maxLa, int maxLb, int smemCand, DevInputs const & in,
-                                cudaStream_t stream, int32_t * workCounter, int gridWarps)
+                                int32_t * finished, int maxLa, int maxLb, int smemCand, DevInputs const & in,
+                                cudaStream_t stream)
 {
     if (n <= 0) return cudaSuccess;
     // one warp (= one pair) per block: pairs differ a lot in run time (finished pairs return at once, alignments
@@ -1190,12 +1199,8 @@ cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state,
     static int const tune = []() { char const * e = std::getenv("LARA_B200_POSTTUNE"); return e ? std::atoi(e) : 0; }();
     size_t const smem = post_smem_per_warp(maxLa, maxLb, smemCand) * warpsPerBlock;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
-    if (workCounter != nullptr && gridWarps > 0 && gridWarps < n)
-        iterate_post_kernel<false, true><<<gridWarps, 32, post_smem_per_warp(maxLa, maxLb, smemCand), stream>>>(
-            n, desc, state, arena, P, outHdr, outLines, outOff, activeCount, maxLa, maxLb, smemCand, tune, in, workCounter);
-    else
-        iterate_post_kernel<false, false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, outHdr, outLines, outOff,
-                                                                                 activeCount, maxLa, maxLb, smemCand, tune, in, nullptr);
+    iterate_post_kernel<false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, pairIdx, desc, state, arena, P, outHdr, outLines, outOff,
+                                                                             finished, maxLa, maxLb, smemCand, tune, in);
     return cudaGetLastError();
 }
 
@@ -1236,8 +1241,8 @@ cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * stat
     DevParams P{};
     P.go = go; P.ge = ge;
     int const blocks = (n + warpsPerBlock - 1) / warpsPerBlock;
-    iterate_post_kernel<true, false><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, desc, state, arena, P, nullptr, nullptr,
-                                                                            nullptr, nullptr, maxLa, maxLb, 0, 0, DevInputs{}, nullptr);
+    iterate_post_kernel<true><<<blocks, warpsPerBlock * 32, smem, stream>>>(n, nullptr, desc, state, arena, P, nullptr, nullptr,
+                                                                            nullptr, nullptr, maxLa, maxLb, 0, 0, DevInputs{});
     return cudaGetLastError();
 }
 

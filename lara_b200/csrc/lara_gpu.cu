@@ -52,8 +52,12 @@ struct OrientedPair
 struct Worker
 {
     cudaStream_t stream = nullptr;
-    int32_t * dActive = nullptr;
-    int32_t * hActive = nullptr;            // pinned
+    int32_t * hFinished = nullptr;          // pinned: two windows of the device's finished list (count + entries)
+    size_t hFinishedCap = 0;
+    cudaEvent_t evBlock[2] = {nullptr, nullptr};   // end of the last two blocks of iteration steps
+    int32_t * hTable = nullptr;             // pinned staging buffer of the slot table
+    size_t hTableCap = 0;
+    cudaEvent_t evTable = nullptr;
     std::vector<cudaEvent_t> events;
     cudaEvent_t evDone = nullptr;
     // side streams: the DP launches of the smaller kernel classes of an iteration run beside the largest one
@@ -115,15 +119,12 @@ struct lara_ctx
     bool bandMode = true;                   // band DP kernels where the active edges allow it (env LARA_B200_BAND=0: off)
     int bandMargin = 1;                     // diagonals added on both sides of the active range (env LARA_B200_MARGIN)
     int bandMaxW = 1024;                    // widest band; beyond it the full-matrix kernel runs (env LARA_B200_BANDMAXW)
-    int bandMinWarps = 400;                 // Q = 16 needs this many warps per launch, else Q = 4 (env LARA_B200_BANDMINWARPS)
+    int bandMinWarps = 600;                 // a batch whose fill has fewer warps than this with blocks of 16 diagonals runs
+                                            // with blocks of 8 and twice the lanes per pair (env LARA_B200_BANDMINWARPS)
+    int band24MinWarps = 64;                // the 24-diagonal shape needs this many warps of its own (env LARA_B200_BAND24MINWARPS)
     bool band24 = true;                     // 24-diagonal one-thread-per-pair shape (env LARA_B200_BAND24=0: off)
-    int postGridPerSm = 0;                  // > 0: post kernel as this many resident one-warp blocks per SM pulling pairs
-                                            // from a counter; < 0: that many warps in total (env LARA_B200_POSTGRID)
     int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
-    bool fillPrio = false;                  // DP launches on high-priority streams (env LARA_B200_FILLPRIO)
     int verbose = 0;                        // env LARA_B200_VERBOSE=1: host-side stage times of every batch on stderr
-    bool compactSlots = false;              // repack the DP slot lists as pairs finish (env LARA_B200_COMPACT=1); measured:
-                                            // the DP is HBM-bound, idle lanes cost nothing, repacking costs locality
     int postSmemCand = 256;                 // matching candidates sorted in shared memory (env LARA_B200_SMEMCAND)
     // host copy of the inputs (for pair orientation and batch sizing)
     int32_t nSeq = 0;
@@ -133,6 +134,8 @@ struct lara_ctx
     bool prepared = false, ran = false;
     lara_stats stats{};
     size_t batchPairsCap = 0;               // test hook: max pairs per batch, 0 = automatic (env LARA_B200_BATCHCAP)
+    int refillMode = 1;                     // slot refill: 0 = set by set, 1 = as slots free up while the queue is long,
+                                            // 2 = always as slots free up (env LARA_B200_REFILL)
     size_t workerMinPairs = 2048;           // a device runs one worker per this many pairs, up to nWorkers (env LARA_B200_WORKERPAIRS)
 };
 
@@ -279,469 +282,598 @@ void choose_band(lara_ctx const & ctx, PairDesc & d, bool allow24)
     d.bandW = W; d.dLo = lo; d.dHi = lo + W - 1;
 }
 
-// Lanes per pair G and diagonals per block Q for the nPairs pairs of a batch that share the band width W:
-// Q = 16 (G = W / 32, down to one thread per pair) when that still fills the machine, else Q = 8 (G = W / 16),
-// else Q = 4 (G = W / 8).
-void choose_band_shape(lara_ctx const & ctx, int W, int nPairs, int & G, int & Q)
+// Lanes per pair G and diagonals per block Q for the pairs of a batch that share the band width W.  One thread walks
+// a block of Q diagonals down the rows as one dependent instruction stream, so the time of a launch is set by Q (measured
+// per row: about 2,000 cycles at Q = 16, 900 at Q = 8, 1,240 at Q = 4 where the hand-off between lanes dominates) as
+// long as the launch does not fill the machine.  batchWarps16 = warps the whole batch would have with blocks of 16: with
+// at least bandMinWarps of them (about one per warp scheduler) the throughput form Q = 16 is used (G = W / 32, down to
+// one thread per pair), else the low-latency form Q = 8 (G = W / 16).  Q = 4 only on request (LARA_B200_BANDQ).
+void choose_band_shape(lara_ctx const & ctx, int W, int64_t batchWarps16, int & G, int & Q)
 {
     if (W == 24) { G = 1; Q = 12; return; }                     // one thread per pair only
-    int const g16 = W / 32, g8 = W / 16, g4 = W / 8;
-    int64_t const warps16 = ((int64_t)nPairs * g16 + 31) / 32, warps8 = ((int64_t)nPairs * g8 + 31) / 32;
-    Q = (g8 > 32 || warps16 >= ctx.bandMinWarps) ? 16 : ((g4 > 32 || warps8 >= ctx.bandMinWarps) ? 8 : 4);
-    if (ctx.bandForceQ == 16 || (ctx.bandForceQ == 8 && W <= 512) || (ctx.bandForceQ == 4 && g4 <= 32)) Q = ctx.bandForceQ;
+    int const g8 = W / 16, g4 = W / 8;
+    Q = (g8 > 32 || batchWarps16 >= ctx.bandMinWarps) ? 16 : 8;
+    if (ctx.bandForceQ == 16 || (ctx.bandForceQ == 8 && g8 <= 32) || (ctx.bandForceQ == 4 && g4 <= 32)) Q = ctx.bandForceQ;
     G = W / (2 * Q);
 }
 
 // ---------------------------------------------------------------------------------------------------
-// One batch: pairs [begin, end) of dv.pairs (already length sorted).  With `pilot` the pairs are pilotPairs[0..n):
-// only the set-up stages up to the counts run, and the densities are returned.
+// The resident set of one worker: the pairs that are iterating on the device right now.
+//
+// The reference keeps `threads` solver slots busy: the moment a pair finishes, its slot takes the next pair of the
+// longest-first queue (src/subgradient_solver.hpp:285-324, SIMD twin src/subgradient_solver_simd.hpp:350-395).  Here
+// a worker holds `capacity` pair slots.  Every iteration step is one DP launch over the slot table plus one post launch;
+// the post kernel appends every pair that finishes to a list, the host reads that list every few steps (without
+// draining the stream: the next steps are already queued), and as soon as a tenth of the slots is free it takes that many
+// pairs from the device's queue (a COHORT), runs their set-up on a side stream while the iteration steps go on, and
+// splices them into the freed slots between two steps.  Every pair carries its own iteration counter
+// (PairState::remaining), so pairs of different cohorts iterate side by side.
+//
+// Slots are positions in BAND GROUPS: the 32 / G pairs that share a warp of the band kernel and its interleaved
+// score / trace arrays (lara_gpu.cuh).  A new pair goes into a free slot of a group of its band width whose arrays
+// are long enough; pairs that find none open new groups.  Per-pair arrays of a cohort are given back when its last
+// pair has finished; the group arrays live as long as the set.
 // ---------------------------------------------------------------------------------------------------
-void run_batch(lara_ctx & ctx, Device & dv, Worker & wk, size_t begin, size_t end, Pilot * pilot = nullptr,
-               OrientedPair const * pilotPairs = nullptr, double slabHintBytes = 0)
+struct BandGroup
 {
-    int const n = (int)(end - begin);
-    // the four big regions of a batch live in the worker's slab: A (length dependent) | S (filter scratch), then B
-    // (per edge, band) and C (per interaction) over S once the filter has run.  A region that does not fit (the
-    // estimate was too low) falls back to the stream-ordered allocator.
-    if (slabHintBytes > 0 && (double)wk.slabInts * 4 < slabHintBytes)
-    {
-        CK(cudaStreamSynchronize(wk.stream));
-        CK(cudaFree(wk.slab));
-        wk.slab = nullptr; wk.slabInts = 0;
-        int64_t const want = ((int64_t)(slabHintBytes * 1.1 / 4) + 1023) & ~(int64_t)1023;
-        CK(cudaMalloc((void **)&wk.slab, (size_t)want * 4));
-        wk.slabInts = want;
-    }
-    std::vector<void *> fallback;
-    auto region_alloc = [&](Region & rg, int64_t sizeInts, int64_t atInts)
-    {
-        if (slabHintBytes > 0 && wk.slab && atInts + sizeInts <= wk.slabInts)
-            rg.ptr = wk.slab + atInts;
-        else
-        {
-            CK(cudaMallocAsync((void **)&rg.ptr, (size_t)std::max<int64_t>(sizeInts, 1) * 4, wk.stream));
-            fallback.push_back(rg.ptr);
-        }
-        rg.size = sizeInts;
-    };
-    auto al256 = [](int64_t x) { return (x + 63) & ~(int64_t)63; };
-    auto tPrev = std::chrono::steady_clock::now();
-    auto lap = [&](char const * what)
-    {
-        if (!ctx.verbose) return;
-        auto const now = std::chrono::steady_clock::now();
-        std::fprintf(stderr, "[lara_b200] dev %d batch %zu+%d %-28s %8.2f ms\n", dv.id, begin, n, what,
-                     std::chrono::duration<double, std::milli>(now - tPrev).count());
-        tPrev = now;
-    };
-    DevParams const & dp = ctx.dp;
-    cudaStream_t const s = wk.stream;
-    std::vector<PairDesc> desc((size_t)n);
+    int G = 0, Q = 0, W = 0, ppw = 0, rows = 0, cols = 0;
+    int64_t ov = 0, ot = 0, ou = 0, ol = 0;     // the group's arrays (offsets in ints from the arena base)
+    std::vector<int32_t> occ;                   // ppw entries: pair (index in the set's pair arrays) or -1
+    int nOcc = 0;
+};
+
+struct Cohort
+{
+    int base = 0, n = 0, live = 0;
     int maxLa = 0, maxLb = 0, maxK = 0;
-    // ---- stage A layout: everything that only depends on the lengths -----------------------------
-    int64_t sizeA = 0;
-    auto layoutA = [&](bool commit, Region & rg)
-    {
-        for (int i = 0; i < n; ++i)
-        {
-            OrientedPair const & op = pilot ? pilotPairs[i] : dv.pairs[begin + i];
-            PairDesc & d = desc[(size_t)i];
-            if (!commit)
-            {
-                std::memset(&d, 0, sizeof(d));
-                d.la = op.la; d.lb = op.lb; d.seqFirst = op.first; d.seqSecond = op.second;
-                d.R = (op.lb + 31) / 32;
-                d.W = d.R <= 8 ? 1 : (d.R <= 16 ? 2 : 4);
-                d.nSteps = (op.la + 31 + 3) & ~3;
-                d.bitWords = (op.lb + 31) / 32;
-                d.kCap = std::min(ctx.nbp[op.first], ctx.nbp[op.second]) + 1;
-                maxLa = std::max(maxLa, d.la); maxLb = std::max(maxLb, d.lb); maxK = std::max(maxK, d.kCap);
-            }
-            d.offBits = rg.take((int64_t)d.la * d.bitWords);
-            d.offRowStart = rg.take(d.la + 1);
-            d.offLines = rg.take(d.lb);
-            d.offBest = rg.take(d.lb);
-            {
-                int64_t capPow2 = 32;                   // the bitonic sort pads to a power of two
-                while (capPow2 < d.kCap) capPow2 <<= 1;
-                d.offCand = rg.take(2 * capPow2);
-            }
-        }
-    };
-    {
-        Region probe;
-        layoutA(false, probe);
-        sizeA = probe.used;
-    }
-    lap("layout A (host)");
-    Region rA;
-    region_alloc(rA, sizeA, 0);
-    int32_t * const arena = rA.ptr;
-    layoutA(true, rA);
+    std::vector<void *> pooled;                 // per-pair arrays from the stream-ordered pool
+};
 
-    // edge filter scratch (forward prefix scores): its own allocation, released right after stage 1
-    Region rS;
-    {
-        int64_t sizeS = 0;
-        for (int i = 0; i < n; ++i) sizeS += align4((int64_t)desc[(size_t)i].la * desc[(size_t)i].lb + 6ll * (desc[(size_t)i].la + 1));
-        region_alloc(rS, sizeS, al256(sizeA));
-        rS.baseDelta = rS.ptr - arena;
-        for (int i = 0; i < n; ++i)
-            desc[(size_t)i].offScratch = rS.take((int64_t)desc[(size_t)i].la * desc[(size_t)i].lb + 6ll * (desc[(size_t)i].la + 1));
-    }
-
+struct ResidentSet
+{
+    lara_ctx & ctx;
+    Device & dv;
+    Worker & wk;
+    cudaStream_t const s;                       // the worker's stream: iteration steps
+    cudaStream_t side = nullptr;                // set-up of the next cohort
+    cudaEvent_t evSide = nullptr;
+    int32_t * arena = nullptr;                  // base of every offset of the set
     PairDesc * dDesc = nullptr;
     PairState * dState = nullptr;
-    CK(cudaMallocAsync((void **)&dDesc, sizeof(PairDesc) * (size_t)n, s));
-    CK(cudaMallocAsync((void **)&dState, sizeof(PairState) * (size_t)n, s));
-    CK(cudaMemsetAsync(dState, 0, sizeof(PairState) * (size_t)n, s));
-    CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
-
-    lap("alloc A + scratch");
-    cudaEvent_t evS0 = wk.events[0], evS1 = wk.events[1];
-    CK(cudaEventRecord(evS0, s));
-    // ---- stage 1: edge filter -> E ------------------------------------------------------------------
-    CK(launch_edge_filter(n, dDesc, dState, arena, dv.in, dp, maxLb, s));
-    CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-    lap("edge filter (sync)");
-    wk.stats.kernel_launches += 1;
-    // ---- stage B layout: per-edge arrays, band geometry and warp groups of the band kernels --------------------
-    std::map<int, std::vector<int32_t>> byW;               // band width -> pairs
-    // the 24-diagonal shape exists as one thread per pair only: used when enough pairs of the batch fit it
-    bool allow24 = false;
-    if (ctx.band24)
-    {
-        int64_t fit = 0;
-        for (int i = 0; i < n; ++i)
-        {
-            choose_band(ctx, desc[(size_t)i], true);
-            fit += desc[(size_t)i].bandW == 24;
-        }
-        allow24 = (fit + 31) / 32 >= ctx.bandMinWarps && ctx.bandForceQ == 0;
-    }
-    for (int i = 0; i < n; ++i)
-    {
-        choose_band(ctx, desc[(size_t)i], allow24);
-        if (desc[(size_t)i].bandW > 0) byW[desc[(size_t)i].bandW].push_back(i);
-    }
-    if (ctx.verbose)
-    {
-        int hist[9] = {0}, fine[4] = {0};
-        for (int i = 0; i < n; ++i)
-        {
-            PairDesc const & d = desc[(size_t)i];
-            int const need = (d.E > 0 && d.dMin <= d.dMax) ? std::max(d.dMax + ctx.bandMargin, 0) - std::min(d.dMin - ctx.bandMargin, 0) + 1 : 1;
-            int b = 0;
-            while (b < 8 && (8 << b) < need) ++b;
-            ++hist[b];
-            if (need > 16 && need <= 32) ++fine[(need - 17) / 4];
-        }
-        std::fprintf(stderr, "[lara_b200]   band need histogram (<=8,16,32,64,128,256,512,1024,more):");
-        for (int b = 0; b < 9; ++b) std::fprintf(stderr, " %d", hist[b]);
-        std::fprintf(stderr, "; 17-20 21-24 25-28 29-32: %d %d %d %d\n", fine[0], fine[1], fine[2], fine[3]);
-    }
-    struct BandClass { int G, Q; std::vector<int32_t> slots; };    // slots: pair index or -1, 32 / G per warp group
-    std::vector<BandClass> bandClasses;
-    struct BandGroup { int W, ppw, rows, cols, first, count; int cls; };
+    size_t pairCap = 0;
+    std::vector<PairDesc> desc;                 // every pair admitted so far, in admission order
+    std::vector<int32_t> cohortOf, groupOf, slotOf;
+    std::vector<uint8_t> finishedHost;
+    std::vector<Cohort> cohorts;
     std::vector<BandGroup> groups;
-    for (auto & kv : byW)
+    std::map<int, std::vector<int32_t>> fullPairs;      // rows per lane R -> pairs of the full-matrix kernel
+    std::vector<void *> keep;                   // allocations that live as long as the set
+    int live = 0;
+    int64_t liveLanes16 = 0;                    // lanes of the live pairs' fill with blocks of 16 diagonals
+    bool have24 = false;
+    // slot table on the device and its launch geometry
+    int32_t * dTable = nullptr;
+    size_t tableCap = 0;
+    int nSlots = 0;
+    std::vector<BandLaunch> bandLaunches;
+    std::vector<std::tuple<int, int, int>> fullLaunches;        // R, offset, count
+    int maxLa = 1, maxLb = 1, smemCand = 32;
+    // finished list: [0] count, [1 ..] pairs
+    int32_t * dFinished = nullptr;
+
+    ResidentSet(lara_ctx & c, Device & d, Worker & w) : ctx(c), dv(d), wk(w), s(w.stream) {}
+
+    void init(size_t maxPairs)
     {
-        int const W = kv.first;
-        std::vector<int32_t> & members = kv.second;
-        std::stable_sort(members.begin(), members.end(), [&](int32_t x, int32_t y) { return desc[(size_t)x].lb > desc[(size_t)y].lb; });
-        int G, Q;
-        choose_band_shape(ctx, W, (int)members.size(), G, Q);
-        int ci = -1;
-        for (size_t k = 0; k < bandClasses.size(); ++k) if (bandClasses[k].G == G && bandClasses[k].Q == Q) ci = (int)k;
-        if (ci < 0) { bandClasses.push_back(BandClass{G, Q, {}}); ci = (int)bandClasses.size() - 1; }
-        int const ppw = 32 / G;
-        for (size_t k = 0; k < members.size(); k += (size_t)ppw)
+        pairCap = std::max<size_t>(maxPairs, 1);
+        CK(cudaMallocAsync((void **)&dDesc, sizeof(PairDesc) * pairCap, s));
+        CK(cudaMallocAsync((void **)&dState, sizeof(PairState) * pairCap, s));
+        CK(cudaMallocAsync((void **)&dFinished, sizeof(int32_t) * (pairCap + 1), s));
+        CK(cudaMemsetAsync(dFinished, 0, sizeof(int32_t), s));
+        CK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&evSide, cudaEventDisableTiming));
+        arena = wk.slab ? wk.slab : reinterpret_cast<int32_t *>(dDesc);
+    }
+
+    void release()
+    {
+        // everything the set still holds; the streams are idle (or the device is in an error state) when this runs
+        cudaStreamSynchronize(s);
+        if (side) cudaStreamSynchronize(side);
+        for (Cohort & c : cohorts) for (void * p : c.pooled) cudaFreeAsync(p, s);
+        for (void * p : keep) cudaFreeAsync(p, s);
+        if (dTable) cudaFreeAsync(dTable, s);
+        if (dFinished) cudaFreeAsync(dFinished, s);
+        if (dState) cudaFreeAsync(dState, s);
+        if (dDesc) cudaFreeAsync(dDesc, s);
+        if (evSide) cudaEventDestroy(evSide);
+        if (side) cudaStreamDestroy(side);
+        cohorts.clear(); keep.clear();
+        dTable = nullptr; dFinished = nullptr; dState = nullptr; dDesc = nullptr; side = nullptr; evSide = nullptr;
+        cudaGetLastError();
+    }
+
+    // ---- set-up of the pairs [begin, end) of the device's queue on stream st ---------------------------------------
+    // Blocks the host twice (edge filter -> E, counts -> D); on return the last set-up kernel is queued on st.  With
+    // `pilot` only the stages up to the counts run and the densities are returned.
+    void admit(size_t begin, size_t end, cudaStream_t st, double slabHintBytes, Pilot * pilot = nullptr,
+               OrientedPair const * pilotPairs = nullptr)
+    {
+        int const n = (int)(end - begin);
+        int const base = (int)desc.size();
+        if ((size_t)base + (size_t)n > pairCap) throw std::runtime_error("resident set: pair arrays too small");
+        bool const useSlab = slabHintBytes > 0 && cohorts.empty() && !pilot;
+        if (useSlab && (double)wk.slabInts * 4 < slabHintBytes)
         {
-            int const cnt = (int)std::min<size_t>((size_t)ppw, members.size() - k);
-            int cols = 0;
-            for (int j = 0; j < cnt; ++j) cols = std::max(cols, desc[(size_t)members[k + (size_t)j]].la + 1);
-            groups.push_back(BandGroup{W, ppw, desc[(size_t)members[k]].lb + 1, cols, (int)bandClasses[(size_t)ci].slots.size(), cnt, ci});
-            for (int j = 0; j < ppw; ++j)
+            CK(cudaStreamSynchronize(s));
+            CK(cudaFree(wk.slab));
+            wk.slab = nullptr; wk.slabInts = 0;
+            int64_t const want = ((int64_t)(slabHintBytes * 1.1 / 4) + 1023) & ~(int64_t)1023;
+            CK(cudaMalloc((void **)&wk.slab, (size_t)want * 4));
+            wk.slabInts = want;
+        }
+        if (cohorts.empty() && !pilot) arena = wk.slab ? wk.slab : reinterpret_cast<int32_t *>(dDesc);
+        cohorts.emplace_back();
+        Cohort * co = &cohorts.back();
+        co->base = base; co->n = n;
+        // a region: part of the worker's slab (first cohort) or a block of the stream-ordered pool
+        auto region_alloc = [&](Region & rg, int64_t sizeInts, int64_t atInts, std::vector<void *> & owner)
+        {
+            if (useSlab && wk.slab && atInts + sizeInts <= wk.slabInts)
+                rg.ptr = wk.slab + atInts;
+            else
             {
-                if (j < cnt)
+                CK(cudaMallocAsync((void **)&rg.ptr, (size_t)std::max<int64_t>(sizeInts, 1) * 4, st));
+                owner.push_back(rg.ptr);
+            }
+            rg.size = sizeInts;
+            rg.baseDelta = rg.ptr - arena;
+        };
+        auto al256 = [](int64_t x) { return (x + 63) & ~(int64_t)63; };
+        auto tPrev = std::chrono::steady_clock::now();
+        auto lap = [&](char const * what)
+        {
+            if (!ctx.verbose) return;
+            auto const now = std::chrono::steady_clock::now();
+            std::fprintf(stderr, "[lara_b200] dev %d cohort %zu+%d %-28s %8.2f ms\n", dv.id, begin, n, what,
+                         std::chrono::duration<double, std::milli>(now - tPrev).count());
+            tPrev = now;
+        };
+        DevParams const & dp = ctx.dp;
+        desc.resize((size_t)base + (size_t)n);
+        cohortOf.resize(desc.size(), (int32_t)cohorts.size() - 1);
+        groupOf.resize(desc.size(), -1);
+        slotOf.resize(desc.size(), -1);
+        finishedHost.resize(desc.size(), 0);
+        PairDesc * const cd = desc.data() + base;             // this cohort's descriptors
+        PairDesc * const dCd = dDesc + base;
+        PairState * const dCs = dState + base;
+        // ---- stage A layout: everything that only depends on the lengths -----------------------------
+        auto layoutA = [&](bool commit, Region & rg)
+        {
+            for (int i = 0; i < n; ++i)
+            {
+                OrientedPair const & op = pilot ? pilotPairs[i] : dv.pairs[begin + (size_t)i];
+                PairDesc & d = cd[i];
+                if (!commit)
                 {
-                    PairDesc & d = desc[(size_t)members[k + (size_t)j]];
-                    d.bandG = G; d.bandQ = Q; d.bandSlot = j;
-                    bandClasses[(size_t)ci].slots.push_back(members[k + (size_t)j]);
+                    std::memset(&d, 0, sizeof(d));
+                    d.la = op.la; d.lb = op.lb; d.seqFirst = op.first; d.seqSecond = op.second;
+                    d.outIdx = (int32_t)(begin + (size_t)i);
+                    d.R = (op.lb + 31) / 32;
+                    d.W = d.R <= 8 ? 1 : (d.R <= 16 ? 2 : 4);
+                    d.nSteps = (op.la + 31 + 3) & ~3;
+                    d.bitWords = (op.lb + 31) / 32;
+                    d.kCap = std::min(ctx.nbp[op.first], ctx.nbp[op.second]) + 1;
+                    co->maxLa = std::max(co->maxLa, d.la); co->maxLb = std::max(co->maxLb, d.lb); co->maxK = std::max(co->maxK, d.kCap);
                 }
-                else
-                    bandClasses[(size_t)ci].slots.push_back(-1);
+                d.offBits = rg.take((int64_t)d.la * d.bitWords);
+                d.offRowStart = rg.take(d.la + 1);
+                d.offLines = rg.take(d.lb);
+                d.offBest = rg.take(d.lb);
+                {
+                    int64_t capPow2 = 32;                   // the bitonic sort pads to a power of two
+                    while (capPow2 < d.kCap) capPow2 <<= 1;
+                    d.offCand = rg.take(2 * capPow2);
+                }
             }
-        }
-    }
-    int64_t sizeB = 0;
-    for (int i = 0; i < n; ++i)
-    {
-        PairDesc & d = desc[(size_t)i];
-        sizeB += 8 * align4(std::max(d.E, 1)) + align4(d.E + 1);
-        if (d.bandW > 0 && d.bandW <= 32) sizeB += align4(4ll * d.la);
-        if (d.bandW == 0)
+        };
+        int64_t sizeA = 0;
         {
-            if (d.R > kMaxR)
-                throw std::runtime_error("a pair whose shorter sequence exceeds " + std::to_string(32 * kMaxR) +
-                                         " nt has active edges on more than " + std::to_string(ctx.bandMaxW) +
-                                         " diagonals: outside the band kernels and the single-pass full-matrix kernel");
-            sizeB += align4(32ll * ((d.nSteps + 31) / 32)) + 32 + align4(32ll * d.nSteps * d.W);
+            Region probe;
+            layoutA(false, probe);
+            sizeA = probe.used;
         }
-    }
-    for (BandGroup const & g : groups)
-        sizeB += align4((int64_t)g.rows * g.W * g.ppw) + (g.ppw == 32 ? (int64_t)((g.rows + 1) & ~1) * 128 + 8 : align4((int64_t)g.rows * (g.W / 8) * g.ppw)) +
-                 4ll * g.ppw * (g.rows + g.cols);
-    lap("layout B (host)");
-    Region rB;
-    region_alloc(rB, sizeB, al256(sizeA));
-    lap("alloc B");
-    rB.baseDelta = rB.ptr - arena;
-    for (int i = 0; i < n; ++i)
-    {
-        PairDesc & d = desc[(size_t)i];
-        d.offCell = rB.take(d.E); d.offSeqScore = rB.take(d.E); d.offPv = rB.take(d.E); d.offPerm = rB.take(d.E);
-        d.offIoff = rB.take(d.E + 1);
-        d.offEdge = rB.take(4ll * d.E);
-        if (d.bandW > 0 && d.bandW <= 32) d.offRowRec = rB.take(4ll * d.la);
-        if (d.bandW > 0)
+        lap("layout A (host)");
+        Region rA;
+        region_alloc(rA, sizeA, 0, co->pooled);
+        layoutA(true, rA);
+        // edge filter scratch (forward prefix scores): lives only until the filter has run
+        Region rS;
+        std::vector<void *> scratchOwner;
         {
-            if (!pilot)
+            int64_t sizeS = 0;
+            for (int i = 0; i < n; ++i) sizeS += align4((int64_t)cd[i].la * cd[i].lb + 6ll * (cd[i].la + 1));
+            region_alloc(rS, sizeS, al256(sizeA), scratchOwner);
+            for (int i = 0; i < n; ++i)
+                cd[i].offScratch = rS.take((int64_t)cd[i].la * cd[i].lb + 6ll * (cd[i].la + 1));
+        }
+        CK(cudaMemsetAsync(dCs, 0, sizeof(PairState) * (size_t)n, st));
+        CK(cudaMemcpyAsync(dCd, cd, sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, st));
+        lap("alloc A + scratch");
+        cudaEvent_t evS0 = wk.events[0], evS1 = wk.events[1];
+        bool const timed = cohorts.size() == 1 && !pilot;       // the first cohort's set-up is timed with events
+        if (timed) CK(cudaEventRecord(evS0, st));
+        // ---- stage 1: edge filter -> E ------------------------------------------------------------------
+        CK(launch_edge_filter(n, dCd, dCs, arena, dv.in, dp, co->maxLb, st));
+        CK(cudaMemcpyAsync(cd, dCd, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        for (void * f : scratchOwner) CK(cudaFreeAsync(f, st));
+        lap("edge filter (sync)");
+        wk.stats.kernel_launches += 1;
+        // ---- band geometry of every pair; slots in existing groups, new groups for the rest ---------------------
+        bool allow24 = false;
+        int64_t batchWarps16 = 0;                               // warps of the set's fill with blocks of 16 diagonals
+        {
+            int64_t fit = 0, lanes16 = liveLanes16;
+            for (int i = 0; i < n; ++i)
             {
-                ++wk.stats.reserved[1];                     // pairs solved by the band kernels
-                if (d.bandQ == 16) ++wk.stats.reserved[2];  // ... of those in blocks of 16 diagonals
-                wk.stats.reserved[3] += d.bandW;            // sum of their band widths
+                choose_band(ctx, cd[i], true);
+                fit += cd[i].bandW == 24;
+                lanes16 += std::max(1, cd[i].bandW / 32);
             }
+            batchWarps16 = (lanes16 + 31) / 32;
+            // the 24-diagonal shape exists as one thread per pair only: used when the set runs in the throughput form and
+            // enough pairs fit it to make a class worth its while
+            allow24 = ctx.band24 && batchWarps16 >= ctx.bandMinWarps && ctx.bandForceQ == 0 &&
+                      (have24 || (fit + 31) / 32 >= ctx.band24MinWarps);
+        }
+        std::map<int, std::vector<int32_t>> byW;               // band width -> pairs (cohort-local index) still without a slot
+        for (int i = 0; i < n; ++i)
+        {
+            choose_band(ctx, cd[i], allow24);
+            if (cd[i].bandW > 0) byW[cd[i].bandW].push_back(i);
+        }
+        if (ctx.verbose)
+        {
+            int hist[9] = {0}, fine[4] = {0};
+            for (int i = 0; i < n; ++i)
+            {
+                PairDesc const & d = cd[i];
+                int const need = (d.E > 0 && d.dMin <= d.dMax) ? std::max(d.dMax + ctx.bandMargin, 0) - std::min(d.dMin - ctx.bandMargin, 0) + 1 : 1;
+                int b = 0;
+                while (b < 8 && (8 << b) < need) ++b;
+                ++hist[b];
+                if (need > 16 && need <= 32) ++fine[(need - 17) / 4];
+            }
+            std::fprintf(stderr, "[lara_b200]   band need histogram (<=8,16,32,64,128,256,512,1024,more):");
+            for (int b = 0; b < 9; ++b) std::fprintf(stderr, " %d", hist[b]);
+            std::fprintf(stderr, "; 17-20 21-24 25-28 29-32: %d %d %d %d\n", fine[0], fine[1], fine[2], fine[3]);
+        }
+        size_t const firstNewGroup = groups.size();
+        int reused = 0;
+        if (!pilot && firstNewGroup > 0)
+        {
+            // free slots of the groups that are there, first fit (groups were opened longest first)
+            std::map<int, std::vector<int>> vacant;                // width -> groups with a free slot
+            for (size_t g = 0; g < groups.size(); ++g)
+                if (groups[g].nOcc < groups[g].ppw) vacant[groups[g].W].push_back((int)g);
+            for (auto & kv : byW)
+            {
+                auto it = vacant.find(kv.first);
+                if (it == vacant.end()) continue;
+                std::vector<int32_t> rest;
+                for (int32_t i : kv.second)
+                {
+                    PairDesc & d = cd[i];
+                    bool placed = false;
+                    for (int g : it->second)
+                    {
+                        BandGroup & bg = groups[(size_t)g];
+                        if (bg.nOcc >= bg.ppw || bg.rows < d.lb + 1 || bg.cols < d.la + 1) continue;
+                        int j = 0;
+                        while (bg.occ[(size_t)j] >= 0) ++j;
+                        bg.occ[(size_t)j] = base + i; ++bg.nOcc;
+                        d.bandG = bg.G; d.bandQ = bg.Q; d.bandSlot = j;
+                        d.offBVals = bg.ov; d.offBTrace = bg.ot; d.offU = bg.ou; d.offL = bg.ol;
+                        groupOf[(size_t)(base + i)] = g; slotOf[(size_t)(base + i)] = j;
+                        placed = true; ++reused;
+                        break;
+                    }
+                    if (!placed) rest.push_back(i);
+                }
+                kv.second.swap(rest);
+            }
+        }
+        for (auto & kv : byW)
+        {
+            int const W = kv.first;
+            std::vector<int32_t> & members = kv.second;
+            if (members.empty()) continue;
+            std::stable_sort(members.begin(), members.end(), [&](int32_t x, int32_t y) { return cd[x].lb > cd[y].lb; });
+            int G, Q;
+            choose_band_shape(ctx, W, batchWarps16, G, Q);
+            int const ppw = 32 / G;
+            for (size_t k = 0; k < members.size(); k += (size_t)ppw)
+            {
+                int const cnt = (int)std::min<size_t>((size_t)ppw, members.size() - k);
+                BandGroup bg;
+                bg.G = G; bg.Q = Q; bg.W = W; bg.ppw = ppw; bg.rows = cd[members[k]].lb + 1;
+                bg.occ.assign((size_t)ppw, -1);
+                for (int j = 0; j < cnt; ++j)
+                {
+                    PairDesc & d = cd[members[k + (size_t)j]];
+                    bg.cols = std::max(bg.cols, d.la + 1);
+                    d.bandG = G; d.bandQ = Q; d.bandSlot = j;
+                    bg.occ[(size_t)j] = base + members[k + (size_t)j];
+                    groupOf[(size_t)(base + members[k + (size_t)j])] = (int32_t)groups.size();
+                    slotOf[(size_t)(base + members[k + (size_t)j])] = j;
+                }
+                bg.nOcc = cnt;
+                groups.push_back(bg);
+            }
+            if (W == 24) have24 = true;
+        }
+        // ---- stage B layout: per-edge arrays (with the cohort), band arrays of the new groups (with the set) ---------
+        int64_t sizeB = 0, sizeG = 0;
+        for (int i = 0; i < n; ++i)
+        {
+            PairDesc & d = cd[i];
+            sizeB += 8 * align4(std::max(d.E, 1)) + align4(d.E + 1);
+            if (d.bandW > 0 && d.bandW <= 32) sizeB += align4(4ll * d.la);
+            if (d.bandW == 0)
+            {
+                if (d.R > kMaxR)
+                    throw std::runtime_error("a pair whose shorter sequence exceeds " + std::to_string(32 * kMaxR) +
+                                             " nt has active edges on more than " + std::to_string(ctx.bandMaxW) +
+                                             " diagonals: outside the band kernels and the single-pass full-matrix kernel");
+                sizeB += align4(32ll * ((d.nSteps + 31) / 32)) + 32 + align4(32ll * d.nSteps * d.W);
+            }
+        }
+        for (size_t g = firstNewGroup; g < groups.size(); ++g)
+        {
+            BandGroup const & bg = groups[g];
+            sizeG += align4((int64_t)bg.rows * bg.W * bg.ppw) + 8 +
+                     (bg.ppw == 32 ? (int64_t)((bg.rows + 1) & ~1) * 128 + 8 : align4((int64_t)bg.rows * (bg.W / 8) * bg.ppw)) +
+                     4ll * bg.ppw * (bg.rows + bg.cols);
+        }
+        lap("layout B (host)");
+        co = &cohorts.back();
+        Region rB, rG;
+        region_alloc(rB, sizeB, al256(sizeA), co->pooled);
+        region_alloc(rG, sizeG, al256(sizeA) + al256(sizeB), pilot ? co->pooled : keep);
+        lap("alloc B");
+        for (int i = 0; i < n; ++i)
+        {
+            PairDesc & d = cd[i];
+            d.offCell = rB.take(d.E); d.offSeqScore = rB.take(d.E); d.offPv = rB.take(d.E); d.offPerm = rB.take(d.E);
+            d.offIoff = rB.take(d.E + 1);
+            d.offEdge = rB.take(4ll * d.E);
+            if (d.bandW > 0 && d.bandW <= 32) d.offRowRec = rB.take(4ll * d.la);
+            if (d.bandW > 0)
+            {
+                if (!pilot)
+                {
+                    ++wk.stats.reserved[1];                     // pairs solved by the band kernels
+                    if (d.bandQ == 16) ++wk.stats.reserved[2];  // ... of those in blocks of 16 diagonals
+                    wk.stats.reserved[3] += d.bandW;            // sum of their band widths
+                }
+            }
+            else
+            {
+                d.offFlags = rB.take(32ll * ((d.nSteps + 31) / 32));
+                d.offLanePtr = rB.take(32);
+                d.offTrace = rB.take(32ll * d.nSteps * d.W);
+            }
+        }
+        for (size_t g = firstNewGroup; g < groups.size(); ++g)
+        {
+            BandGroup & bg = groups[g];
+            bg.ov = rG.take((int64_t)bg.rows * bg.W * bg.ppw);
+            // trace: W / 8 ints per row and pair; one thread per pair (ppw 32, W 32 or 24): 16-byte row records, two
+            // rows per 32-byte sector
+            if (bg.ppw == 32) rG.used = (rG.used + 7) & ~(int64_t)7;
+            bg.ot = bg.ppw == 32 ? rG.take((int64_t)((bg.rows + 1) & ~1) * 4 * 32)
+                                 : rG.take((int64_t)bg.rows * (bg.W / 8) * bg.ppw);
+            bg.ou = rG.take(4ll * bg.ppw * bg.rows);
+            bg.ol = rG.take(4ll * bg.ppw * bg.cols);
+            for (int j = 0; j < bg.ppw; ++j)
+                if (bg.occ[(size_t)j] >= 0)
+                {
+                    PairDesc & d = desc[(size_t)bg.occ[(size_t)j]];
+                    d.offBVals = bg.ov; d.offBTrace = bg.ot; d.offU = bg.ou; d.offL = bg.ol;
+                }
+        }
+        CK(cudaMemcpyAsync(dCd, cd, sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, st));
+        // ---- stage 2: counts -> D, nVals -----------------------------------------------------------------------
+        CK(launch_setup_count(n, dCd, dCs, arena, dv.in, dp, st));
+        CK(cudaMemcpyAsync(cd, dCd, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        lap("set-up count (sync)");
+        wk.stats.kernel_launches += 1;
+        if (pilot)
+        {
+            for (int i = 0; i < n; ++i)
+            {
+                PairDesc const & d = cd[i];
+                pilot->cells += (double)d.la * d.lb;
+                pilot->edges += d.E;
+                pilot->inters += d.D;
+                // scores + trace + closed-form records of the band, or stream + trace of the full-matrix kernel
+                pilot->dpBytes += d.bandW > 0 ? 4.6 * d.bandW * (d.lb + 1) + 16.0 * (d.la + d.lb + 2)
+                                              : 4.0 * d.nVals + 128.0 * d.nSteps * d.W;
+            }
+            return;
+        }
+        int64_t sizeC = 0;
+        for (int i = 0; i < n; ++i) sizeC += 14 * align4(std::max(cd[i].D, 1)) + 20 + align4(std::max(cd[i].nVals, 1));
+        Region rC;
+        region_alloc(rC, sizeC, al256(sizeA) + al256(sizeB) + al256(sizeG), co->pooled);
+        lap("alloc C");
+        for (int i = 0; i < n; ++i)
+        {
+            PairDesc & d = cd[i];
+            d.offPart = rC.take(d.D); d.offPpos = rC.take(d.D); d.offSc = rC.take(d.D); d.offDual = rC.take(d.D);
+            d.offRev = rC.take(d.D); d.offList = rC.take(d.D); d.offVals = rC.take(d.nVals);
+            rC.used = (rC.used + 15) & ~(int64_t)15;          // hot records: rows start on 64-byte fetch units where they can
+            d.offInter = rC.take(4ll * d.D);
+            d.offInterCold = rC.take(4ll * d.D);
+            wk.stats.n_active_edges += d.E; wk.stats.n_interactions += d.D;
+            wk.stats.filter_cells += 2ll * d.la * d.lb;
+            if (d.bandW == 0) fullPairs[d.R].push_back(base + i);
+            liveLanes16 += std::max(1, d.bandW / 32);
+        }
+        CK(cudaMemcpyAsync(dCd, cd, sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, st));
+        // ---- stage 3: fill ---------------------------------------------------------------------------------------
+        CK(launch_setup_fill(n, dCd, dCs, arena, dv.in, dp, st));
+        wk.stats.kernel_launches += 1;
+        if (timed) CK(cudaEventRecord(evS1, st));
+        co->live = n;
+        live += n;
+        wk.stats.n_pairs += n;
+        if (cohorts.size() == 1)
+        {
+            // algorithmic HBM bytes of one DP launch with every pair of the first cohort live (bench.py: traffic probe)
+            int64_t bytes = 0, pairs = 0;
+            for (int i = 0; i < n; ++i)
+                if (cd[i].bandW > 0) { bytes += (int64_t)(4.5 * cd[i].bandW * cd[i].lb + 16.0 * (cd[i].la + cd[i].lb + 2)); ++pairs; }
+            wk.stats.reserved[10] = bytes; wk.stats.reserved[11] = pairs;
         }
         else
-        {
-            d.offFlags = rB.take(32ll * ((d.nSteps + 31) / 32));
-            d.offLanePtr = rB.take(32);
-            d.offTrace = rB.take(32ll * d.nSteps * d.W);
-        }
+            wk.stats.reserved[12] += n;                       // pairs taken into a running set
+        if (ctx.verbose)
+            std::fprintf(stderr, "[lara_b200] dev %d cohort %zu+%d: %d into free slots, %zu new groups, %d pairs live\n", dv.id, begin, n,
+                         reused, groups.size() - firstNewGroup, live);
     }
-    for (BandGroup const & g : groups)
-    {
-        int64_t const ov = rB.take((int64_t)g.rows * g.W * g.ppw);
-        // trace: W / 8 ints per row and pair; one thread per pair (ppw 32, W 32 or 24): 16-byte row records, two
-        // rows per 32-byte sector
-        if (g.ppw == 32) rB.used = (rB.used + 7) & ~(int64_t)7;
-        int64_t const ot = g.ppw == 32 ? rB.take((int64_t)((g.rows + 1) & ~1) * 4 * 32)
-                                       : rB.take((int64_t)g.rows * (g.W / 8) * g.ppw);
-        int64_t const ou = rB.take(4ll * g.ppw * g.rows);
-        int64_t const ol = rB.take(4ll * g.ppw * g.cols);
-        for (int j = 0; j < g.count; ++j)
-        {
-            PairDesc & d = desc[(size_t)bandClasses[(size_t)g.cls].slots[(size_t)(g.first + j)]];
-            d.offBVals = ov; d.offBTrace = ot; d.offU = ou; d.offL = ol;
-        }
-    }
-    CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
-    // ---- stage 2: counts -> D, nVals -----------------------------------------------------------------------
-    CK(launch_setup_count(n, dDesc, dState, arena, dv.in, dp, s));
-    CK(cudaMemcpyAsync(desc.data(), dDesc, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-    lap("set-up count (sync)");
-    wk.stats.kernel_launches += 1;
-    if (pilot)
-    {
-        for (int i = 0; i < n; ++i)
-        {
-            PairDesc const & d = desc[(size_t)i];
-            pilot->cells += (double)d.la * d.lb;
-            pilot->edges += d.E;
-            pilot->inters += d.D;
-            // scores + trace + closed-form records of the band, or stream + trace of the full-matrix kernel
-            pilot->dpBytes += d.bandW > 0 ? 4.6 * d.bandW * (d.lb + 1) + 16.0 * (d.la + d.lb + 2)
-                                          : 4.0 * d.nVals + 128.0 * d.nSteps * d.W;
-        }
-        for (void * f : fallback) CK(cudaFreeAsync(f, s));
-        CK(cudaFreeAsync(dState, s));
-        CK(cudaFreeAsync(dDesc, s));
-        CK(cudaStreamSynchronize(s));
-        return;
-    }
-    int64_t sizeC = 0;
-    for (int i = 0; i < n; ++i) sizeC += 14 * align4(std::max(desc[(size_t)i].D, 1)) + 20 + align4(std::max(desc[(size_t)i].nVals, 1));
-    Region rC;
-    region_alloc(rC, sizeC, al256(sizeA) + al256(sizeB));
-    lap("alloc C");
-    rC.baseDelta = rC.ptr - arena;
-    for (int i = 0; i < n; ++i)
-    {
-        PairDesc & d = desc[(size_t)i];
-        d.offPart = rC.take(d.D); d.offPpos = rC.take(d.D); d.offSc = rC.take(d.D); d.offDual = rC.take(d.D);
-        d.offRev = rC.take(d.D); d.offList = rC.take(d.D); d.offVals = rC.take(d.nVals);
-        rC.used = (rC.used + 15) & ~(int64_t)15;          // hot records: rows start on 64-byte fetch units where they can
-        d.offInter = rC.take(4ll * d.D);
-        d.offInterCold = rC.take(4ll * d.D);
-        wk.stats.n_active_edges += d.E; wk.stats.n_interactions += d.D;
-        wk.stats.filter_cells += 2ll * d.la * d.lb;
-    }
-    CK(cudaMemcpyAsync(dDesc, desc.data(), sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, s));
-    // ---- stage 3: fill ---------------------------------------------------------------------------------------
-    CK(launch_setup_fill(n, dDesc, dState, arena, dv.in, dp, s));
-    wk.stats.kernel_launches += 1;
-    CK(cudaEventRecord(evS1, s));
 
-    // ---- launch classes of the DP: rows per lane R (full-matrix kernel) or band shape (G, Q) ----------------------
-    std::map<int, std::vector<int32_t>> classes;
-    for (int i = 0; i < n; ++i)
-        if (desc[(size_t)i].bandW == 0) classes[desc[(size_t)i].R].push_back(i);
-    std::vector<int32_t> idxAll;
-    std::vector<std::tuple<int, int, int, int>> cls;   // R (or 0), offset, count, band class
-    for (auto & kv : classes)
+    // ---- slot table: the occupied groups class by class (most slots first), then the full-matrix classes -----------
+    void rebuild_table()
     {
-        cls.emplace_back(kv.first, (int)idxAll.size(), (int)kv.second.size(), -1);
-        idxAll.insert(idxAll.end(), kv.second.begin(), kv.second.end());
-    }
-    for (size_t k = 0; k < bandClasses.size(); ++k)
-    {
-        cls.emplace_back(0, (int)idxAll.size(), (int)bandClasses[k].slots.size(), (int)k);
-        idxAll.insert(idxAll.end(), bandClasses[k].slots.begin(), bandClasses[k].slots.end());
-    }
-    std::stable_sort(cls.begin(), cls.end(), [](auto const & x, auto const & y) { return std::get<2>(x) > std::get<2>(y); });
-    if (ctx.verbose)
-        for (auto const & c : cls)
+        std::map<std::pair<int, int>, std::vector<int>> byShape;        // (G, Q) -> groups with a pair in them
+        for (size_t g = 0; g < groups.size(); ++g)
+            if (groups[g].nOcc > 0) byShape[{groups[g].G, groups[g].Q}].push_back((int)g);
+        std::vector<std::tuple<int64_t, int, int>> order;              // slots, G, Q
+        for (auto const & kv : byShape) order.emplace_back((int64_t)kv.second.size() * (32 / kv.first.first), kv.first.first, kv.first.second);
+        std::sort(order.begin(), order.end(), [](auto const & x, auto const & y) { return std::get<0>(x) > std::get<0>(y); });
+        std::vector<int32_t> table;
+        bandLaunches.clear(); fullLaunches.clear();
+        for (auto const & o : order)
         {
-            if (std::get<3>(c) >= 0)
-                std::fprintf(stderr, "[lara_b200]   DP class band G=%d Q=%d (W=%d): %d slots\n", bandClasses[(size_t)std::get<3>(c)].G,
-                             bandClasses[(size_t)std::get<3>(c)].Q, 2 * bandClasses[(size_t)std::get<3>(c)].G * bandClasses[(size_t)std::get<3>(c)].Q,
-                             std::get<2>(c));
-            else
-                std::fprintf(stderr, "[lara_b200]   DP class full matrix R=%d: %d pairs\n", std::get<0>(c), std::get<2>(c));
+            int const G = std::get<1>(o), Q = std::get<2>(o);
+            int const off = (int)table.size();
+            for (int g : byShape[{G, Q}])
+                table.insert(table.end(), groups[(size_t)g].occ.begin(), groups[(size_t)g].occ.end());
+            bandLaunches.push_back(BandLaunch{G, Q, (int)table.size() - off, off});
         }
-    if (!wk.evFork) CK(cudaEventCreateWithFlags(&wk.evFork, cudaEventDisableTiming));
-    // fillPrio: every DP launch runs on a high-priority side stream, so that its few, long-running blocks are placed as
-    // soon as blocks of the other worker's post kernel retire instead of queueing behind all of them
-    size_t const auxBase = ctx.fillPrio ? 0 : 1;                  // class k runs on aux[k - auxBase] (k < auxBase: on s)
-    while (wk.aux.size() + auxBase < cls.size())
-    {
-        cudaStream_t st; cudaEvent_t ev;
-        int prLo = 0, prHi = 0;
-        CK(cudaDeviceGetStreamPriorityRange(&prLo, &prHi));
-        CK(cudaStreamCreateWithPriority(&st, cudaStreamNonBlocking, ctx.fillPrio ? prHi : prLo));
-        CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-        wk.aux.push_back(st); wk.auxJoin.push_back(ev);
-    }
-    // two copies of the slot lists (the DP launches read one, a compaction writes the other) + one counter per class
-    int32_t * dIdx = nullptr;
-    size_t const idxStride = std::max<size_t>(idxAll.size(), 1);
-    int const nIter = ctx.P.num_iterations;
-    size_t const nCtr = ctx.postGridPerSm != 0 ? (size_t)nIter : 0;        // one work counter per post launch
-    CK(cudaMallocAsync((void **)&dIdx, sizeof(int32_t) * (2 * idxStride + cls.size() + 1 + nCtr), s));
-    CK(cudaMemcpyAsync(dIdx, idxAll.data(), sizeof(int32_t) * idxAll.size(), cudaMemcpyHostToDevice, s));
-    int32_t * const dCounts = dIdx + 2 * idxStride;
-    int32_t * const dPostCtr = nCtr ? dCounts + cls.size() + 1 : nullptr;
-    if (nCtr) CK(cudaMemsetAsync(dPostCtr, 0, sizeof(int32_t) * nCtr, s));
-    std::vector<int> clsSide(cls.size(), 0), clsCount(cls.size());
-    std::vector<int32_t> hCounts(cls.size());
-    for (size_t k = 0; k < cls.size(); ++k) clsCount[k] = std::get<2>(cls[k]);
-    int lastCompactActive = n;
-    *wk.hActive = n;
-    CK(cudaMemcpyAsync(wk.dActive, wk.hActive, sizeof(int32_t), cudaMemcpyHostToDevice, s));
-
-    // shared memory candidates: as many as fit next to the line arrays (cap 2048)
-    int smemCand = 32;
-    while (smemCand < maxK && smemCand < ctx.postSmemCand) smemCand <<= 1;
-
-    // ---- the subgradient loop -------------------------------------------------------------------------------------
-    size_t const needEv = 2 + 3 * (size_t)nIter;
-    while (wk.events.size() < needEv)
-    {
-        cudaEvent_t e;
-        CK(cudaEventCreate(&e));
-        wk.events.push_back(e);
-    }
-    int itersRun = 0;
-    int nextPoll = 1;
-    for (int it = 0; it < nIter; ++it)
-    {
-        CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it], s));
-        // the largest class on the worker's stream, the others beside it on side streams (fork / join by events)
-        if (cls.size() > auxBase) CK(cudaEventRecord(wk.evFork, s));
-        for (size_t k = 0; k < cls.size(); ++k)
+        for (auto & kv : fullPairs)
         {
-            auto const & c = cls[k];
-            cudaStream_t const sk = k < auxBase ? s : wk.aux[k - auxBase];
-            if (k >= auxBase) CK(cudaStreamWaitEvent(sk, wk.evFork, 0));
-            int32_t const * const lst = dIdx + (size_t)clsSide[k] * idxStride + std::get<1>(c);
-            if (clsCount[k] == 0) continue;
-            if (std::get<3>(c) >= 0)
-                CK(launch_gotoh_band(bandClasses[(size_t)std::get<3>(c)].G, bandClasses[(size_t)std::get<3>(c)].Q, clsCount[k],
-                                     lst, dDesc, dState, arena, dp.go, dp.ge, sk));
-            else
-                CK(launch_gotoh_fill(std::get<0>(c), clsCount[k], lst, dDesc, dState, arena, dv.negBuf, dp.go, dp.ge, sk));
-            if (k >= auxBase) CK(cudaEventRecord(wk.auxJoin[k - auxBase], sk));
+            std::vector<int32_t> & v = kv.second;
+            v.erase(std::remove_if(v.begin(), v.end(), [&](int32_t p) { return finishedHost[(size_t)p] != 0; }), v.end());
+            if (v.empty()) continue;
+            fullLaunches.emplace_back(kv.first, (int)table.size(), (int)v.size());
+            table.insert(table.end(), v.begin(), v.end());
+        }
+        nSlots = (int)table.size();
+        if (table.size() > tableCap)
+        {
+            if (dTable) CK(cudaFreeAsync(dTable, s));
+            tableCap = table.size() + table.size() / 4 + 1024;
+            CK(cudaMallocAsync((void **)&dTable, sizeof(int32_t) * tableCap, s));
+        }
+        if (!table.empty())
+        {
+            // through a page-locked buffer: a copy from pageable memory would drain the stream first
+            if (wk.hTableCap < table.size())
+            {
+                if (wk.hTable) { CK(cudaStreamSynchronize(s)); CK(cudaFreeHost(wk.hTable)); }
+                wk.hTableCap = table.size() + table.size() / 4 + 1024;
+                CK(cudaMallocHost((void **)&wk.hTable, sizeof(int32_t) * wk.hTableCap));
+            }
+            if (!wk.evTable) CK(cudaEventCreateWithFlags(&wk.evTable, cudaEventDisableTiming));
+            else CK(cudaEventSynchronize(wk.evTable));                  // the previous upload has left the buffer
+            std::memcpy(wk.hTable, table.data(), sizeof(int32_t) * table.size());
+            CK(cudaMemcpyAsync(dTable, wk.hTable, sizeof(int32_t) * table.size(), cudaMemcpyHostToDevice, s));
+            CK(cudaEventRecord(wk.evTable, s));
+        }
+        maxLa = 1; maxLb = 1;
+        int maxK = 1;
+        for (Cohort const & c : cohorts)
+            if (c.live > 0) { maxLa = std::max(maxLa, c.maxLa); maxLb = std::max(maxLb, c.maxLb); maxK = std::max(maxK, c.maxK); }
+        // shared memory candidates of the matching: as many as fit next to the line arrays (cap 2048)
+        smemCand = 32;
+        while (smemCand < maxK && smemCand < ctx.postSmemCand) smemCand <<= 1;
+        if (ctx.verbose)
+        {
+            for (BandLaunch const & b : bandLaunches)
+                std::fprintf(stderr, "[lara_b200]   DP class band G=%d Q=%d (W=%d): %d slots\n", b.G, b.Q, 2 * b.G * b.Q, b.nSlots);
+            for (auto const & f : fullLaunches)
+                std::fprintf(stderr, "[lara_b200]   DP class full matrix R=%d: %d pairs\n", std::get<0>(f), std::get<2>(f));
+        }
+    }
+
+    // a pair the device reported as finished: its slot and, with the last pair of its cohort, the cohort's arrays are free
+    void on_finished(int p)
+    {
+        if (p < 0 || (size_t)p >= desc.size() || finishedHost[(size_t)p]) return;
+        finishedHost[(size_t)p] = 1;
+        --live;
+        liveLanes16 -= std::max(1, desc[(size_t)p].bandW / 32);
+        int const g = groupOf[(size_t)p];
+        if (g >= 0)
+        {
+            BandGroup & bg = groups[(size_t)g];
+            bg.occ[(size_t)slotOf[(size_t)p]] = -1;
+            --bg.nOcc;
+        }
+        Cohort & c = cohorts[(size_t)cohortOf[(size_t)p]];
+        if (--c.live == 0)
+        {
+            for (void * f : c.pooled) CK(cudaFreeAsync(f, s));
+            c.pooled.clear();
+        }
+    }
+
+    // one iteration step: DP launch(es) + post launch
+    void enqueue_step(cudaEvent_t e0, cudaEvent_t e1, cudaEvent_t e2)
+    {
+        DevParams const & dp = ctx.dp;
+        CK(cudaEventRecord(e0, s));
+        // full-matrix classes (pairs without a usable band) on side streams, all band classes in one launch
+        if (!fullLaunches.empty())
+        {
+            if (!wk.evFork) CK(cudaEventCreateWithFlags(&wk.evFork, cudaEventDisableTiming));
+            while (wk.aux.size() < fullLaunches.size())
+            {
+                cudaStream_t st; cudaEvent_t ev;
+                CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+                CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+                wk.aux.push_back(st); wk.auxJoin.push_back(ev);
+            }
+            CK(cudaEventRecord(wk.evFork, s));
+            for (size_t k = 0; k < fullLaunches.size(); ++k)
+            {
+                CK(cudaStreamWaitEvent(wk.aux[k], wk.evFork, 0));
+                CK(launch_gotoh_fill(std::get<0>(fullLaunches[k]), std::get<2>(fullLaunches[k]), dTable + std::get<1>(fullLaunches[k]),
+                                     dDesc, dState, arena, dv.negBuf, dp.go, dp.ge, wk.aux[k]));
+                CK(cudaEventRecord(wk.auxJoin[k], wk.aux[k]));
+                wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
+            }
+        }
+        if (!bandLaunches.empty())
+        {
+            CK(launch_gotoh_band_multi((int)bandLaunches.size(), bandLaunches.data(), dTable, dDesc, dState, arena, dp.go, dp.ge, s));
             wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
         }
-        for (size_t k = auxBase; k < cls.size(); ++k) CK(cudaStreamWaitEvent(s, wk.auxJoin[k - auxBase], 0));
-        CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 1], s));
-        CK(launch_iterate_post(n, dDesc, dState, arena, dp, dv.dOutHdr + begin, dv.dOutLines, dv.dOutOff + begin,
-                               wk.dActive, maxLa, maxLb, smemCand, dv.in, s, nCtr ? dPostCtr + it : nullptr,
-                               ctx.postGridPerSm > 0 ? ctx.postGridPerSm * dv.smCount : -ctx.postGridPerSm));
+        for (size_t k = 0; k < fullLaunches.size(); ++k) CK(cudaStreamWaitEvent(s, wk.auxJoin[k], 0));
+        CK(cudaEventRecord(e1, s));
+        CK(launch_iterate_post(nSlots, dTable, dDesc, dState, arena, dp, dv.dOutHdr, dv.dOutLines, dv.dOutOff, dFinished,
+                               maxLa, maxLb, smemCand, dv.in, s));
         wk.stats.kernel_launches += 1;
-        CK(cudaEventRecord(wk.events[2 + 3 * (size_t)it + 2], s));
-        itersRun = it + 1;
-        if (it + 1 == nextPoll && it + 1 < nIter)
-        {
-            CK(cudaMemcpyAsync(wk.hActive, wk.dActive, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
-            CK(cudaStreamSynchronize(s));
-            if (*wk.hActive <= 0) break;
-            // finished pairs leave holes in the warps of the DP kernels: repack the slot lists now and then
-            if (ctx.compactSlots && (int64_t)*wk.hActive * 10 < (int64_t)lastCompactActive * 9)
-            {
-                CK(cudaMemsetAsync(dCounts, 0, sizeof(int32_t) * cls.size(), s));
-                for (size_t k = 0; k < cls.size(); ++k)
-                    CK(launch_compact_slots(clsCount[k], dIdx + (size_t)clsSide[k] * idxStride + std::get<1>(cls[k]), dState,
-                                            dIdx + (size_t)(1 - clsSide[k]) * idxStride + std::get<1>(cls[k]), dCounts + k, s));
-                CK(cudaMemcpyAsync(hCounts.data(), dCounts, sizeof(int32_t) * cls.size(), cudaMemcpyDeviceToHost, s));
-                CK(cudaStreamSynchronize(s));
-                for (size_t k = 0; k < cls.size(); ++k) { clsSide[k] = 1 - clsSide[k]; clsCount[k] = hCounts[k]; }
-                wk.stats.kernel_launches += (int64_t)cls.size();
-                lastCompactActive = *wk.hActive;
-            }
-            nextPoll = nextPoll < 16 ? nextPoll * 2 : nextPoll + 16;
-        }
+        CK(cudaEventRecord(e2, s));
+        wk.stats.reserved[7] += 1;
+        wk.stats.reserved[8] += nSlots;
     }
-    lap("iterations (enqueue + polls)");
-    // error flags
-    std::vector<PairState> hState((size_t)n);
-    CK(cudaMemcpyAsync(hState.data(), dState, sizeof(PairState) * (size_t)n, cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-    for (int i = 0; i < n; ++i)
-    {
-        if (hState[(size_t)i].error)
-            throw std::runtime_error("internal invariant violated on the device (code " +
-                                     std::to_string(hState[(size_t)i].error) + ")");
-        if (!hState[(size_t)i].done)
-            throw std::runtime_error("pair did not finish within numIterations");
-        int64_t const its = ctx.P.num_iterations - hState[(size_t)i].remaining;
-        wk.stats.sum_iterations += its;
-        wk.stats.dp_cells += its * (int64_t)desc[(size_t)i].la * desc[(size_t)i].lb;
-        {
-            // algorithmic HBM bytes of the DP launches: band: 4 B score + 0.5 B trace per band cell and
-            // 16 B closed-form record per row and column; full matrix: 1.3 B per cell (sparse stream + trace)
-            PairDesc const & d = desc[(size_t)i];
-            wk.stats.reserved[4] += d.bandW > 0 ? its * (int64_t)(4.5 * d.bandW * d.lb + 16.0 * (d.la + d.lb + 2))
-                                                : its * (int64_t)(1.3 * d.la * d.lb);
-            wk.stats.reserved[5] += d.bandW > 0 ? its * (int64_t)d.bandW * d.lb : its * (int64_t)d.la * d.lb;   // cells computed
-        }
-    }
-    wk.stats.ms_setup += ev_ms(evS0, evS1);
-    for (int it = 0; it < itersRun; ++it)
-    {
-        wk.stats.ms_dp += ev_ms(wk.events[2 + 3 * (size_t)it], wk.events[2 + 3 * (size_t)it + 1]);
-        wk.stats.ms_bounds += ev_ms(wk.events[2 + 3 * (size_t)it + 1], wk.events[2 + 3 * (size_t)it + 2]);
-    }
-    wk.stats.n_pairs += n;
-    wk.stats.reserved[6] += 1;                                  // batches run
-    CK(cudaFreeAsync(dIdx, s));
-    for (void * f : fallback) CK(cudaFreeAsync(f, s));
-    CK(cudaFreeAsync(dState, s));
-    CK(cudaFreeAsync(dDesc, s));
-}
+};
 
 // Pairs per batch from the free device memory and a per-pair estimate (exact for the length dependent
 // part, heuristic for the edge/interaction arrays whose sizes are only known after set-up).
@@ -759,7 +891,7 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers, doub
     size_t hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : ctx.batchPairsDefault;
     if (!ctx.batchPairsCap)
     {
-        // equal batches, a multiple of the worker count of them, so that no worker ends with a small batch alone
+        // equal shares, a multiple of the worker count of them, so that no worker ends with a small set alone
         size_t const N = dv.pairs.size();
         size_t nB = (N + hardCap - 1) / hardCap;
         nB = (nB + (size_t)nWorkers - 1) / (size_t)nWorkers * (size_t)nWorkers;
@@ -784,24 +916,165 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers, doub
     return k;
 }
 
+// One worker: a resident set that is refilled from the device's queue until the queue is empty and the last pair has
+// finished.
 void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
 {
+    ResidentSet rs(ctx, dv, wk);
     try
     {
         CK(cudaSetDevice(dv.id));
-        for (;;)
+        cudaStream_t const s = wk.stream;
+        size_t begin, end;
+        double bytes = 0;
         {
-            size_t begin, end;
-            double bytes = 0;
-            {
-                std::lock_guard<std::mutex> lock(dv.queueMutex);
-                begin = dv.nextBegin;
-                if (begin >= dv.pairs.size()) break;
-                end = batch_limit(ctx, dv, begin, nWorkers, bytes);
-                dv.nextBegin = end;
-            }
-            run_batch(ctx, dv, wk, begin, end, nullptr, nullptr, bytes);
+            std::lock_guard<std::mutex> lock(dv.queueMutex);
+            begin = dv.nextBegin;
+            end = begin < dv.pairs.size() ? batch_limit(ctx, dv, begin, nWorkers, bytes) : begin;
+            dv.nextBegin = end;
         }
+        if (end > begin)
+        {
+            size_t const capacity = end - begin;
+            rs.init(dv.pairs.size());
+            rs.admit(begin, end, s, bytes);
+            rs.rebuild_table();
+            int const nIter = ctx.P.num_iterations;
+            // finished list window read by the host after every block of steps: [0] count, [1 ..] the entries from
+            // the host's read position on
+            size_t const window = std::min<size_t>(dv.pairs.size(), 65536);
+            if (wk.hFinishedCap < 2 * (window + 1))
+            {
+                if (wk.hFinished) CK(cudaFreeHost(wk.hFinished));
+                CK(cudaMallocHost((void **)&wk.hFinished, sizeof(int32_t) * 2 * (window + 1)));
+                wk.hFinishedCap = 2 * (window + 1);
+            }
+            if (!wk.evBlock[0]) for (int k = 0; k < 2; ++k) CK(cudaEventCreateWithFlags(&wk.evBlock[k], cudaEventDisableTiming));
+            size_t readPos = 0;                             // finished entries the host has processed
+            size_t winStart[2] = {0, 0};
+            int steps = 0, block = 0, nextBlockLen = 1;
+            // every set may run numIterations steps, and its end is noticed up to two blocks of steps late
+            int64_t const maxSteps = ((int64_t)nIter + 64) * (int64_t)(dv.pairs.size() / capacity + 3) + 64;
+            bool more = true;                               // the queue may still hold pairs
+            bool pendingSplice = false;
+            int outstanding = -1;                           // buffer of the block whose results have not been read yet
+            for (;;)
+            {
+                // ---- queue a block of steps ----------------------------------------------------------------------
+                int const len = nextBlockLen;
+                nextBlockLen = std::min(16, nextBlockLen * 2);
+                while (wk.events.size() < 2 + 3 * (size_t)(steps + len))
+                {
+                    cudaEvent_t e;
+                    CK(cudaEventCreate(&e));
+                    wk.events.push_back(e);
+                }
+                if (pendingSplice)
+                {
+                    // the pairs whose set-up ran on the side stream join between two steps
+                    CK(cudaStreamWaitEvent(s, rs.evSide, 0));
+                    rs.rebuild_table();
+                    pendingSplice = false;
+                }
+                for (int k = 0; k < len; ++k, ++steps)
+                    rs.enqueue_step(wk.events[2 + 3 * (size_t)steps], wk.events[2 + 3 * (size_t)steps + 1], wk.events[2 + 3 * (size_t)steps + 2]);
+                int const cur = block & 1;
+                int32_t * const hb = wk.hFinished + (size_t)cur * (window + 1);
+                winStart[cur] = readPos;
+                CK(cudaMemcpyAsync(hb, rs.dFinished, sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+                CK(cudaMemcpyAsync(hb + 1, rs.dFinished + 1 + readPos, sizeof(int32_t) * std::min(window, rs.pairCap - readPos),
+                                   cudaMemcpyDeviceToHost, s));
+                CK(cudaEventRecord(wk.evBlock[cur], s));
+                ++block;
+                // ---- results of the block before this one (the device is busy with the block just queued) ---------------
+                auto read_block = [&](int b)
+                {
+                    CK(cudaEventSynchronize(wk.evBlock[b]));
+                    int32_t const * const rb = wk.hFinished + (size_t)b * (window + 1);
+                    size_t const count = (size_t)rb[0];
+                    size_t const from = std::max(readPos, winStart[b]);
+                    size_t const to = std::min(count, winStart[b] + window);
+                    for (size_t k = from; k < to; ++k) rs.on_finished(rb[1 + (k - winStart[b])]);
+                    if (to > readPos) readPos = to;
+                };
+                if (outstanding >= 0) read_block(outstanding);
+                outstanding = cur;
+                // ---- refill: a tenth of the slots free (or nothing left to iterate) and pairs waiting -----------------------
+                if (more && !pendingSplice)
+                {
+                    size_t const freeSlots = capacity > (size_t)rs.live ? capacity - (size_t)rs.live : 0;
+                    // Eager refill keeps every slot busy, but a pair taken in late runs up to numIterations steps beyond
+                    // the pairs that were there before it: when the queue is about to run dry that only stretches the
+                    // tail (measured on C3, where three pairs in four use all 500 iterations: 2,110 steps instead of
+                    // 2,000).  So slots are refilled as they free up while the queue still holds more than two full
+                    // rounds of all workers' sets, and set by set (when the set has drained) after that.
+                    size_t queued;
+                    {
+                        std::lock_guard<std::mutex> lock(dv.queueMutex);
+                        queued = dv.pairs.size() - std::min(dv.pairs.size(), dv.nextBegin);
+                    }
+                    bool const eager = ctx.refillMode == 2 || (ctx.refillMode == 1 && queued > 2 * capacity * (size_t)nWorkers);
+                    if ((eager && freeSlots >= std::max<size_t>(capacity / 10, 1)) || rs.live == 0)
+                    {
+                        size_t b2, e2;
+                        {
+                            std::lock_guard<std::mutex> lock(dv.queueMutex);
+                            b2 = dv.nextBegin;
+                            e2 = std::min(dv.pairs.size(), b2 + std::max<size_t>(freeSlots, 1));
+                            dv.nextBegin = e2;
+                        }
+                        if (e2 > b2)
+                        {
+                            // the slots are known to be free: their pairs were reported by a block that has completed
+                            rs.admit(b2, e2, rs.side, 0);
+                            CK(cudaEventRecord(rs.evSide, rs.side));
+                            pendingSplice = true;
+                        }
+                        else
+                            more = false;
+                    }
+                }
+                if (rs.live == 0 && !pendingSplice && !more)
+                {
+                    // every pair is accounted for; the block just queued finds nothing to do
+                    read_block(outstanding);
+                    break;
+                }
+                if (steps > maxSteps) throw std::runtime_error("pairs did not finish within the iteration limit");
+            }
+            CK(cudaStreamSynchronize(s));
+            // ---- per-pair outcome: error flags, iteration counts, work counters --------------------------------------------
+            size_t const nAll = rs.desc.size();
+            std::vector<PairState> hState(nAll);
+            CK(cudaMemcpyAsync(hState.data(), rs.dState, sizeof(PairState) * nAll, cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            for (size_t i = 0; i < nAll; ++i)
+            {
+                if (hState[i].error)
+                    throw std::runtime_error("internal invariant violated on the device (code " + std::to_string(hState[i].error) +
+                                             ") in pair (" + std::to_string(rs.desc[i].seqFirst) + ", " + std::to_string(rs.desc[i].seqSecond) + ")");
+                if (!hState[i].done)
+                    throw std::runtime_error("pair did not finish within numIterations");
+                int64_t const its = ctx.P.num_iterations - hState[i].remaining;
+                PairDesc const & d = rs.desc[i];
+                wk.stats.sum_iterations += its;
+                wk.stats.reserved[9] += its;
+                wk.stats.dp_cells += its * (int64_t)d.la * d.lb;
+                // algorithmic HBM bytes of the DP launches: band: 4 B score + 0.5 B trace per band cell and
+                // 16 B closed-form record per row and column; full matrix: 1.3 B per cell (sparse stream + trace)
+                wk.stats.reserved[4] += d.bandW > 0 ? its * (int64_t)(4.5 * d.bandW * d.lb + 16.0 * (d.la + d.lb + 2))
+                                                    : its * (int64_t)(1.3 * d.la * d.lb);
+                wk.stats.reserved[5] += d.bandW > 0 ? its * (int64_t)d.bandW * d.lb : its * (int64_t)d.la * d.lb;   // cells computed
+            }
+            wk.stats.ms_setup += ev_ms(wk.events[0], wk.events[1]);
+            for (int it = 0; it < steps; ++it)
+            {
+                wk.stats.ms_dp += ev_ms(wk.events[2 + 3 * (size_t)it], wk.events[2 + 3 * (size_t)it + 1]);
+                wk.stats.ms_bounds += ev_ms(wk.events[2 + 3 * (size_t)it + 1], wk.events[2 + 3 * (size_t)it + 2]);
+            }
+            wk.stats.reserved[6] += (int64_t)rs.cohorts.size();           // cohorts (the first one + refills)
+        }
+        rs.release();
         CK(cudaEventRecord(wk.evDone, wk.stream));
         CK(cudaStreamSynchronize(wk.stream));
     }
@@ -809,6 +1082,7 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
     {
         wk.err = e.what();
         cudaGetLastError();
+        rs.release();
     }
 }
 
@@ -831,7 +1105,14 @@ void run_device(lara_ctx & ctx, Device & dv)
             std::vector<OrientedPair> sample(nS);
             for (size_t i = 0; i < nS; ++i) sample[i] = dv.pairs[i * dv.pairs.size() / nS];
             lara_stats const keep = dv.workers[0].stats;
-            run_batch(ctx, dv, dv.workers[0], 0, nS, &dv.pilot, sample.data());
+            ResidentSet probe(ctx, dv, dv.workers[0]);
+            try
+            {
+                probe.init(nS);
+                probe.admit(0, nS, dv.workers[0].stream, 0, &dv.pilot, sample.data());
+            }
+            catch (...) { probe.release(); throw; }
+            probe.release();
             dv.workers[0].stats = keep;
         }
         CK(cudaEventRecord(dv.evRun0, dv.stream));
@@ -864,12 +1145,9 @@ void run_device(lara_ctx & ctx, Device & dv)
         dv.stats.reserved[0] = nW;
         for (int w = 0; w < nW; ++w)
         {
-            dv.stats.reserved[1] += dv.workers[(size_t)w].stats.reserved[1];
-            dv.stats.reserved[2] += dv.workers[(size_t)w].stats.reserved[2];
-            dv.stats.reserved[3] += dv.workers[(size_t)w].stats.reserved[3];
-            dv.stats.reserved[4] += dv.workers[(size_t)w].stats.reserved[4];
-            dv.stats.reserved[5] += dv.workers[(size_t)w].stats.reserved[5];
-            dv.stats.reserved[6] += dv.workers[(size_t)w].stats.reserved[6];
+            lara_stats const & ws = dv.workers[(size_t)w].stats;
+            for (int k : {1, 2, 3, 4, 5, 6, 7, 8, 9, 12}) dv.stats.reserved[k] += ws.reserved[k];
+            if (ws.reserved[11] > dv.stats.reserved[11]) { dv.stats.reserved[10] = ws.reserved[10]; dv.stats.reserved[11] = ws.reserved[11]; }
         }
     }
     catch (std::exception const & e)
@@ -951,14 +1229,13 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_BANDMAXW")) ctx->bandMaxW = std::max(0, std::min(1024, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BANDMINWARPS")) ctx->bandMinWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BAND24")) ctx->band24 = std::atoi(e) != 0;
+    if (char const * e = std::getenv("LARA_B200_BAND24MINWARPS")) ctx->band24MinWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BANDQ")) ctx->bandForceQ = std::atoi(e);
-    if (char const * e = std::getenv("LARA_B200_POSTGRID")) ctx->postGridPerSm = std::max(-4096, std::min(32, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_VERBOSE")) ctx->verbose = std::atoi(e);
-    if (char const * e = std::getenv("LARA_B200_FILLPRIO")) ctx->fillPrio = std::atoi(e) != 0;
-    if (char const * e = std::getenv("LARA_B200_COMPACT")) ctx->compactSlots = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_SMEMCAND")) ctx->postSmemCand = std::max(32, std::min(2048, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BATCHCAP")) ctx->batchPairsCap = (size_t)std::max(0, std::atoi(e));
+    if (char const * e = std::getenv("LARA_B200_REFILL")) ctx->refillMode = std::max(0, std::min(2, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_WORKERPAIRS")) ctx->workerMinPairs = (size_t)std::max(1, std::atoi(e));
     ctx->P = *params;
     ctx->dp = make_dev_params(*params);
@@ -980,8 +1257,6 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
                 dv.workers.emplace_back();
                 Worker & wk = dv.workers.back();
                 CK(cudaStreamCreateWithFlags(&wk.stream, cudaStreamNonBlocking));
-                CK(cudaMalloc((void **)&wk.dActive, sizeof(int32_t)));
-                CK(cudaMallocHost((void **)&wk.hActive, sizeof(int32_t)));
                 CK(cudaEventCreateWithFlags(&wk.evDone, cudaEventDisableTiming));
                 for (int k = 0; k < 2; ++k)
                 {
@@ -1062,8 +1337,10 @@ void lara_gpu_destroy(lara_ctx * ctx)
         if (dv.evRun1) cudaEventDestroy(dv.evRun1);
         for (Worker & wk : dv.workers)
         {
-            cudaFree(wk.dActive);
-            if (wk.hActive) cudaFreeHost(wk.hActive);
+            if (wk.hFinished) cudaFreeHost(wk.hFinished);
+            if (wk.hTable) cudaFreeHost(wk.hTable);
+            if (wk.evTable) cudaEventDestroy(wk.evTable);
+            for (int k = 0; k < 2; ++k) if (wk.evBlock[k]) cudaEventDestroy(wk.evBlock[k]);
             for (cudaEvent_t ev : wk.events) cudaEventDestroy(ev);
             if (wk.evDone) cudaEventDestroy(wk.evDone);
             if (wk.evFork) cudaEventDestroy(wk.evFork);
@@ -1254,12 +1531,11 @@ int lara_gpu_run_prepared(lara_ctx * ctx)
         agg.n_pairs += dv.stats.n_pairs; agg.sum_iterations += dv.stats.sum_iterations;
         agg.n_active_edges += dv.stats.n_active_edges; agg.n_interactions += dv.stats.n_interactions;
         agg.reserved[0] = std::max(agg.reserved[0], dv.stats.reserved[0]);     // concurrent workers per device
-        agg.reserved[1] += dv.stats.reserved[1];                               // pairs solved by the band kernels
-        agg.reserved[2] += dv.stats.reserved[2];                               // ... in blocks of 16 diagonals
-        agg.reserved[3] += dv.stats.reserved[3];                               // sum of the band widths
-        agg.reserved[4] += dv.stats.reserved[4];                               // algorithmic HBM bytes of the DP launches
-        agg.reserved[5] += dv.stats.reserved[5];                               // DP cells actually computed
-        agg.reserved[6] += dv.stats.reserved[6];                               // batches run
+        // [1] pairs solved by the band kernels, [2] ... in blocks of 16 diagonals, [3] sum of the band widths, [4] algorithmic
+        // HBM bytes of the DP launches, [5] DP cells actually computed, [6] cohorts, [7] iteration steps, [8] slots of
+        // the steps, [9] live slots of the steps, [12] pairs taken into running sets
+        for (int k : {1, 2, 3, 4, 5, 6, 7, 8, 9, 12}) agg.reserved[k] += dv.stats.reserved[k];
+        if (dv.stats.reserved[11] > agg.reserved[11]) { agg.reserved[10] = dv.stats.reserved[10]; agg.reserved[11] = dv.stats.reserved[11]; }
     }
     agg.ms_total = ms;
     ctx->stats = agg;

@@ -58,6 +58,8 @@ struct PairDesc
     int32_t nVals;              // entries of the strip-dense pssm stream
     int32_t bitWords;           // words per row of the active bitmap: ceil(lb / 32)
     int32_t kCap;               // upper bound of matching candidates per iteration
+    int32_t outIdx;             // position of the pair in the device's prepared pair list (== its result slot)
+    int32_t pad0_;
     int64_t offBits;            // active bitmap   [la][bitWords]
     int64_t offRowStart;        // first compact edge id of bitmap row a  [la + 1]
     int64_t offFlags;           // per lane step flags: bit (t & 31) of word [lane][t >> 5], nFlagWords words per lane
@@ -159,20 +161,30 @@ cudaError_t launch_gotoh_fill(int R, int n, int32_t const * pairIdx, PairDesc co
 cudaError_t launch_gotoh_band(int G, int Q, int nSlots, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t go, int32_t ge, cudaStream_t stream);
 bool band_shape_supported(int G, int Q);
-// out = the entries p >= 0 of in[0..n) whose pair has not finished, *count += their number (count zeroed by the caller)
-cudaError_t launch_compact_slots(int n, int32_t const * in, PairState const * state, int32_t * out, int32_t * count,
-                                 cudaStream_t stream);
+// all band shapes of a batch in one launch: class k works on pairIdx[slotOffset .. slotOffset + nSlots)
+constexpr int kMaxBandClasses = 16;
+struct BandLaunch { int G, Q, nSlots, slotOffset; };
+struct BandClassTable
+{
+    int32_t n;
+    int32_t shape[kMaxBandClasses];             // (G << 8) | Q
+    int32_t firstBlock[kMaxBandClasses + 1];    // first block of the class's part of the grid
+    int32_t slotOffset[kMaxBandClasses];
+    int32_t nSlots[kMaxBandClasses];
+};
+cudaError_t launch_gotoh_band_multi(int nClasses, BandLaunch const * cls, int32_t const * pairIdx, PairDesc const * desc,
+                                    PairState * state, int32_t * arena, int32_t go, int32_t ge, cudaStream_t stream);
 // position (in ints, relative to offBVals) of the score of band cell (row r, diagonal index x)
 __host__ __device__ inline int64_t band_val_index(int bandW, int ppw, int slot, int r, int x)
 {
     return (((int64_t)r * (bandW >> 2) + (x >> 2)) * ppw + slot) * 4 + (x & 3);
 }
-// traceback + valid_solution + matching + bounds + update for all n pairs of the batch.  With a work counter (zero
-// before the launch) and gridWarps < n the grid is gridWarps one-warp blocks that pull pairs from the counter.
-cudaError_t launch_iterate_post(int n, PairDesc const * desc, PairState * state, int32_t * arena,
+// traceback + valid_solution + matching + bounds + update for the pairs in the n slots of the batch's slot table
+// (pairIdx; -1 = empty slot).  finished[0] counts the pairs that have finished, finished[1 ..] lists them.
+cudaError_t launch_iterate_post(int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
                                 DevParams const & P, PairOutHdr * outHdr, int32_t * outLines, int64_t const * outOff,
-                                int32_t * activeCount, int maxLa, int maxLb, int smemCand, DevInputs const & in,
-                                cudaStream_t stream, int32_t * workCounter = nullptr, int gridWarps = 0);
+                                int32_t * finished, int maxLa, int maxLb, int smemCand, DevInputs const & in,
+                                cudaStream_t stream);
 // traceback only (unit entry point lara_gpu_gotoh_batch)
 cudaError_t launch_traceback_only(int n, PairDesc const * desc, PairState * state, int32_t * arena,
                                   int32_t go, int32_t ge, int maxLa, int maxLb, cudaStream_t stream);

@@ -32,7 +32,7 @@ def test_struct_sizes_match_header(built):
     from lara_b200 import _lib
     assert C.sizeof(_lib.LaraParams) == 4 * 4 + 4 * 4 + 2 * 4 + 25 * 4 + 3 * 4 + 9 * 4
     assert C.sizeof(_lib.LaraPairResult) == 32
-    assert C.sizeof(_lib.LaraStats) == 7 * 8 + 10 * 8 + 8 + 7 * 8
+    assert C.sizeof(_lib.LaraStats) == 7 * 8 + 10 * 8 + 8 + 16 * 8
     assert _lib.load().lara_gpu_version() == 1
 
 

@@ -95,16 +95,16 @@ def test_solve_skewed_lengths(built):
     dict(LARA_B200_BANDQ="4"),
     dict(LARA_B200_BANDQ="8"),
     dict(LARA_B200_BANDQ="16"),
-    dict(LARA_B200_BANDQ="16", LARA_B200_COMPACT="1", LARA_B200_BATCH="40", LARA_B200_WORKERS="3"),
+    dict(LARA_B200_BANDQ="16", LARA_B200_BATCHCAP="20", LARA_B200_WORKERPAIRS="20", LARA_B200_WORKERS="3"),
     dict(LARA_B200_BANDMAXW="32", LARA_B200_BATCH="33"),
     dict(LARA_B200_BANDMINWARPS="1"),                   # lets the 24-diagonal one-thread shape in on a small batch
     dict(LARA_B200_BAND24="0", LARA_B200_BANDMINWARPS="1"),
-    dict(LARA_B200_POSTGRID="-7"),                      # post kernel as 7 resident warps pulling pairs from a counter
-    dict(LARA_B200_POSTGRID="-5", LARA_B200_WORKERS="2", LARA_B200_BATCH="40"),
+    dict(LARA_B200_BANDMINWARPS="100000"),              # low-latency form: blocks of 8 diagonals, twice the lanes per pair
+    dict(LARA_B200_BANDMINWARPS="1", LARA_B200_BATCHCAP="16", LARA_B200_REFILL="2"),   # 16 slots refilled as pairs finish
 ])
 def test_solve_kernel_variants(built, env, monkeypatch):
     """Every DP kernel family and the scheduling switches give the same bits: full matrix, band blocks of 4 / 8 / 16
-    diagonals, compacted slot lists, several small batches on concurrent workers, band / full-matrix mixes."""
+    diagonals, small resident sets refilled from the queue on concurrent workers, band / full-matrix mixes."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     files = util.make_input(seed=39, n=12, length=90, lenmax=200)
@@ -113,21 +113,26 @@ def test_solve_kernel_variants(built, env, monkeypatch):
 
 
 @pytest.mark.parametrize("env,workers", [
-    (dict(LARA_B200_BATCHCAP="30", LARA_B200_WORKERPAIRS="60"), 2),
-    (dict(LARA_B200_BATCHCAP="24", LARA_B200_WORKERPAIRS="40", LARA_B200_WORKERS="3", LARA_B200_COMPACT="1"), 3),
-    (dict(LARA_B200_BATCHCAP="50", LARA_B200_WORKERPAIRS="1000"), 1),
+    (dict(LARA_B200_BATCHCAP="30", LARA_B200_WORKERPAIRS="60", LARA_B200_REFILL="2"), 2),
+    (dict(LARA_B200_BATCHCAP="24", LARA_B200_WORKERPAIRS="40", LARA_B200_WORKERS="3", LARA_B200_REFILL="2"), 3),
+    (dict(LARA_B200_BATCHCAP="50", LARA_B200_WORKERPAIRS="1000", LARA_B200_REFILL="2"), 1),
+    (dict(LARA_B200_BATCHCAP="20", LARA_B200_WORKERPAIRS="1000", LARA_B200_REFILL="1"), 1),      # eager first, set by set at the end
+    (dict(LARA_B200_BATCHCAP="40", LARA_B200_WORKERPAIRS="80", LARA_B200_REFILL="0"), 2),        # set by set only
 ])
 def test_solve_many_batches_per_worker(built, env, workers, monkeypatch):
-    """Concurrent workers that each run several batches through their reused slab (the configuration behind the
-    headline numbers: C3 = 4 batches on 2 workers): 231 pairs in batches of 24..50 on 1..3 workers."""
+    """Concurrent workers whose resident sets (24..50 slots) are refilled many times from the shared queue while
+    they iterate: 231 pairs on 1..3 workers.  Pairs of different cohorts iterate side by side in one slot table, new
+    pairs take the band-group slots of finished ones."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     files = util.make_input(seed=43, n=22, length=70, lenmax=150)
     got, want, st = _solve_both(files, num_iterations=60, max_nondecreasing=8)
     assert util.results_equal(got, want) is None, util.results_equal(got, want)
     assert st.reserved[0] == workers
-    assert st.reserved[6] >= 231 // int(env["LARA_B200_BATCHCAP"])          # batches run
+    assert st.reserved[6] >= 231 // int(env["LARA_B200_BATCHCAP"])          # cohorts: first fill + refills
     assert st.reserved[6] >= 3 * workers
+    assert st.reserved[12] > 0                                               # pairs taken into a running or drained set
+    assert st.reserved[9] == st.sum_iterations and 0 < st.reserved[9] <= st.reserved[8]
 
 
 def _solve_store(store, **kw):
