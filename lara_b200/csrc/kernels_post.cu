@@ -238,6 +238,70 @@ __device__ int traceback_walk(PairDesc const & d, PairState const & st, int32_t 
     return n;
 }
 
+// Traceback + evaluateLines over the dense decision matrix of the row-by-row kernel (kernels_rows.cu: one byte per cell):
+// the plain walk of dp_traceback_impl.h:190-418, every lane the same steps (the pairs that come here are few and long).
+__device__ int traceback_dense(PairDesc const & d, PairState const & st, int32_t const * __restrict__ arena,
+                               int32_t go, int32_t ge, uint32_t * linesRev, int32_t & gapOut, int lane)
+{
+    uint8_t const * __restrict__ tr = reinterpret_cast<uint8_t const *>(arena + d.offTrace);
+    size_t const ncol = (size_t)d.la + 1;
+    int c = d.la, r = d.lb;
+    int n = 0;
+    int32_t gap = 0;
+    int prev = 0;
+    int const endFix = (st.vEnd == st.sEnd) ? 1 : ((st.hEnd == st.sEnd) ? 2 : 0);
+    bool first = true;
+    while (c > 0 && r > 0)
+    {
+        uint32_t nib = tr[(size_t)r * ncol + c];
+        if (first)
+        {
+            if (endFix == 1) nib = (nib | kTrGap) & ~kTrFromH;
+            else if (endFix == 2) nib = nib | kTrGap | kTrFromH;
+            first = false;
+        }
+        if (!(nib & kTrGap))
+        {
+            if (lane == 0) linesRev[n] = ((uint32_t)(c - 1) << 16) | (uint32_t)(r - 1);
+            ++n; --c; --r; prev = 0;
+        }
+        else if (!(nib & kTrFromH))
+        {
+            // vertical run: cells that extended V, closed by the cell that opened it (or by row 1)
+            int steps = 0;
+            for (;;)
+            {
+                uint32_t const x = tr[(size_t)(r - steps) * ncol + c];
+                bool const ext = !(x & kTrVOpen) && (r - steps) != 1;
+                ++steps;
+                if (!ext) break;
+            }
+            gap += ((prev == 1) ? ge : go) + (steps - 1) * ge;
+            prev = 1;
+            r -= steps;
+        }
+        else
+        {
+            int steps = 0;
+            for (;;)
+            {
+                uint32_t const x = tr[(size_t)r * ncol + (c - steps)];
+                bool const ext = !(x & kTrHOpen) && (c - steps) != 1;
+                ++steps;
+                if (!ext) break;
+            }
+            gap += ((prev == 2) ? ge : go) + (steps - 1) * ge;
+            prev = 2;
+            c -= steps;
+        }
+    }
+    if (r > 0) { gap += ((prev == 1) ? ge : go) + (r - 1) * ge; prev = 1; }
+    if (c > 0) { gap += ((prev == 2) ? ge : go) + (c - 1) * ge; prev = 2; }
+    __syncwarp();
+    gapOut = gap;
+    return n;
+}
+
 // ---- band mode (kernels_band.cu) ---------------------------------------------------------------------------
 // Trace decisions of ANY cell of the matrix: inside the band from the stored nibbles, outside from the closed
 // forms of the pure gap regions U (c - r > dHi) and L (c - r < dLo); see tools/band_proto.py (u_nib / l_nib).
@@ -734,6 +798,8 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         }
         nLines = traceback_band(bv, sE, vE, hE, sm.linesRev, sm.win, gapScore, lane);
     }
+    else if (d.dense)
+        nLines = traceback_dense(d, st, arena, P.go, P.ge, sm.linesRev, gapScore, lane);
     else
         nLines = traceback_walk(d, st, arena, P.go, P.ge, sm.linesRev, sm.win, gapScore, lane);
     if (lane == 0) { sm.misc[0] = 0; sm.misc[1] = 0; sm.misc[2] = 0; sm.misc[11] = 0; }
@@ -1024,13 +1090,20 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
     finished = __shfl_sync(kFull, finished, 0);
 
     // ---- 7. multiplier update (:267-271) -----------------------------------------------------------
+    // Bit 30 of a list entry records whether the multiplier went DOWN.  With a positive step that is the +1 entry of a
+    // pair and never the -1 entry, but the step can be negative (the bounds may cross, and the SIMD build's int32
+    // product wraps: src/subgradient_solver_simd.hpp:313) and the float round trip of a large multiplier can move it
+    // either way, so the direction is taken from the values.
     for (int i = lane; i < nList; i += 32)
     {
         uint32_t const x = (uint32_t)list[i];
-        size_t const di = (size_t)(x & 0x7fffffffu);
+        size_t const di = (size_t)(x & 0x3fffffffu);
         int32_t * const dual = &reinterpret_cast<int32_t *>(inter + di)[3];
-        float const f = __int2float_rn(*dual);
-        *dual = __float2int_rz((x >> 31) ? __fadd_rn(f, stepSize) : __fsub_rn(f, stepSize));
+        int32_t const before = *dual;
+        float const f = __int2float_rn(before);
+        int32_t const after = __float2int_rz((x >> 31) ? __fadd_rn(f, stepSize) : __fsub_rn(f, stepSize));
+        *dual = after;
+        list[i] = (int32_t)((x & 0xbfffffffu) | (after < before ? 0x40000000u : 0u));
     }
     __syncwarp();
 
@@ -1039,16 +1112,16 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         // ---- 8a. updateScores (:312-323): refresh the queue top of every touched edge -------------
         int32_t * __restrict__ vals = arena + (d.bandW > 0 ? d.offBVals : d.offVals);
         int32_t const * __restrict__ perm = arena + d.offPerm;
-        // The list holds pairs (x, reverse of x): the multiplier of x went down (x was a tied top of its row, so the
-        // row's maximum has to be found again), the multiplier of the reverse entry went up (its row's maximum can
-        // only grow: max(top, new value), an atomic that commutes with the plain store of a full rescan of the row).
+        // A multiplier that went down may have been the maximum of its row (the +1 entries were tied tops): the row's
+        // maximum has to be found again.  A multiplier that went up can only raise its row's maximum: max(top, new
+        // value), an atomic that commutes with the plain store of a full rescan of the same row.
         int const nPairs = nList >> 1;
         if (tune & 2)
         {
             // measurement switch: every entry rescans its row (the round-1d form)
             for (int i = lane; i < nList; i += 32)
             {
-                size_t const di = (size_t)((uint32_t)list[i] & 0x7fffffffu);
+                size_t const di = (size_t)((uint32_t)list[i] & 0x3fffffffu);
                 int const l = cold[di].z;
                 int4 const er = edge[l];
                 int32_t const sq = er.x;
@@ -1065,28 +1138,40 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         }
         for (int k = lane; k < nPairs; k += 32)
         {
-            size_t const di = (size_t)((uint32_t)list[2 * k] & 0x7fffffffu);
-            int const l = cold[di].z;              // owner of interaction di
-            int4 const er = edge[l];
-            int32_t const sq = er.x;
-            int32_t top = sq;
-            #pragma unroll 4
-            for (int x = er.z; x < er.z + er.w; ++x)
+            #pragma unroll
+            for (int h = 0; h < 2; ++h)
             {
-                int4 const r0 = inter[(size_t)x];
-                top = max(top, sq + r0.z + r0.w);
+                uint32_t const le = (uint32_t)list[2 * k + h];
+                if (!(le & 0x40000000u)) continue;
+                size_t const di = (size_t)(le & 0x3fffffffu);
+                int const l = cold[di].z;                   // owner of interaction di
+                int4 const er = edge[l];
+                int32_t const sq = er.x;
+                int32_t top = sq;
+                #pragma unroll 4
+                for (int x = er.z; x < er.z + er.w; ++x)
+                {
+                    int4 const r0 = inter[(size_t)x];
+                    top = max(top, sq + r0.z + r0.w);
+                }
+                reinterpret_cast<int32_t *>(edge + l)[1] = top;
+                vals[perm[l]] = top;
             }
-            reinterpret_cast<int32_t *>(edge + l)[1] = top;
-            vals[perm[l]] = top;
         }
         for (int k = lane; k < nPairs; k += 32)
         {
-            size_t const di = (size_t)((uint32_t)list[2 * k + 1] & 0x7fffffffu);
-            int4 const r0 = inter[di];
-            int const l = cold[di].z;
-            int32_t const v = edge[l].x + r0.z + r0.w;
-            atomicMax(&reinterpret_cast<int32_t *>(edge + l)[1], v);
-            atomicMax(&vals[perm[l]], v);
+            #pragma unroll
+            for (int h = 0; h < 2; ++h)
+            {
+                uint32_t const le = (uint32_t)list[2 * k + h];
+                if (le & 0x40000000u) continue;
+                size_t const di = (size_t)(le & 0x3fffffffu);
+                int4 const r0 = inter[di];
+                int const l = cold[di].z;
+                int32_t const v = edge[l].x + r0.z + r0.w;
+                atomicMax(&reinterpret_cast<int32_t *>(edge + l)[1], v);
+                atomicMax(&vals[perm[l]], v);
+            }
         }
         return;
     }

@@ -335,6 +335,12 @@ setup_count_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__
         if (lane == 0) d.nVals = 0;
         return;
     }
+    if (d.dense)
+    {
+        // row-by-row kernel: dense (lb + 1) x (la + 1) score array
+        if (lane == 0) d.nVals = (lb + 1) * (la + 1);
+        return;
+    }
     // full-matrix mode: strip-dense stream: step flags per lane, stream start per lane
     int const nFlagWords = (d.nSteps + 31) >> 5;
     uint32_t * __restrict__ flags = (uint32_t *)(arena + d.offFlags) + (size_t)lane * nFlagWords;
@@ -427,6 +433,21 @@ setup_fill_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__ 
             int const ab = cell[e];
             int const a = ab >> 16, b = ab & 0xffff;
             int const idx = (int)band_val_index(d.bandW, ppw, d.bandSlot, b + 1, a - b - d.dLo);
+            vals[idx] = pv[e];
+            perm[e] = idx;
+        }
+    }
+    else if (d.dense)
+    {
+        // dense array of the row-by-row kernel: cell (c, r) = (a + 1, b + 1) at r * (la + 1) + c
+        int const ncol = la + 1;
+        int const total = (lb + 1) * ncol;
+        for (int i = lane; i < total; i += 32) vals[i] = kDpNeg;
+        __syncwarp();
+        for (int e = lane; e < E; e += 32)
+        {
+            int const ab = cell[e];
+            int const idx = ((ab & 0xffff) + 1) * ncol + (ab >> 16) + 1;
             vals[idx] = pv[e];
             perm[e] = idx;
         }

@@ -121,6 +121,7 @@ struct lara_ctx
     int bandMaxW = 1024;                    // widest band; beyond it the full-matrix kernel runs (env LARA_B200_BANDMAXW)
     int bandMinWarps = 600;                 // a batch whose fill has fewer warps than this with blocks of 16 diagonals runs
                                             // with blocks of 8 and twice the lanes per pair (env LARA_B200_BANDMINWARPS)
+    int bandClassMinWarps = 64;             // ... and a width class of fewer warps than this too (env LARA_B200_BANDCLASSMINWARPS)
     int band24MinWarps = 64;                // the 24-diagonal shape needs this many warps of its own (env LARA_B200_BAND24MINWARPS)
     bool band24 = true;                     // 24-diagonal one-thread-per-pair shape (env LARA_B200_BAND24=0: off)
     int bandForceQ = 0;                     // 4 / 16: fixed block size (env LARA_B200_BANDQ)
@@ -134,6 +135,7 @@ struct lara_ctx
     bool prepared = false, ran = false;
     lara_stats stats{};
     size_t batchPairsCap = 0;               // test hook: max pairs per batch, 0 = automatic (env LARA_B200_BATCHCAP)
+    bool forceRows = false;                 // every pair without a band runs the row-by-row kernel (env LARA_B200_ROWS=1; tests)
     int refillMode = 1;                     // slot refill: 0 = set by set, 1 = as slots free up while the queue is long,
                                             // 2 = always as slots free up (env LARA_B200_REFILL)
     size_t workerMinPairs = 2048;           // a device runs one worker per this many pairs, up to nWorkers (env LARA_B200_WORKERPAIRS)
@@ -288,11 +290,14 @@ void choose_band(lara_ctx const & ctx, PairDesc & d, bool allow24)
 // long as the launch does not fill the machine.  batchWarps16 = warps the whole batch would have with blocks of 16: with
 // at least bandMinWarps of them (about one per warp scheduler) the throughput form Q = 16 is used (G = W / 32, down to
 // one thread per pair), else the low-latency form Q = 8 (G = W / 16).  Q = 4 only on request (LARA_B200_BANDQ).
-void choose_band_shape(lara_ctx const & ctx, int W, int64_t batchWarps16, int & G, int & Q)
+void choose_band_shape(lara_ctx const & ctx, int W, int64_t batchWarps16, int64_t classWarps16, int & G, int & Q)
 {
     if (W == 24) { G = 1; Q = 12; return; }                     // one thread per pair only
     int const g8 = W / 16, g4 = W / 8;
-    Q = (g8 > 32 || batchWarps16 >= ctx.bandMinWarps) ? 16 : 8;
+    // all shapes of a set share one launch, which lasts as long as its slowest class: a class of a few warps (the
+    // handful of C3 pairs that need 64 diagonals) takes the low-latency form even in a big set
+    bool const throughput = batchWarps16 >= ctx.bandMinWarps && classWarps16 >= ctx.bandClassMinWarps;
+    Q = (g8 > 32 || throughput) ? 16 : 8;
     if (ctx.bandForceQ == 16 || (ctx.bandForceQ == 8 && g8 <= 32) || (ctx.bandForceQ == 4 && g4 <= 32)) Q = ctx.bandForceQ;
     G = W / (2 * Q);
 }
@@ -592,7 +597,7 @@ struct ResidentSet
             if (members.empty()) continue;
             std::stable_sort(members.begin(), members.end(), [&](int32_t x, int32_t y) { return cd[x].lb > cd[y].lb; });
             int G, Q;
-            choose_band_shape(ctx, W, batchWarps16, G, Q);
+            choose_band_shape(ctx, W, batchWarps16, ((int64_t)members.size() * std::max(1, W / 32) + 31) / 32, G, Q);
             int const ppw = 32 / G;
             for (size_t k = 0; k < members.size(); k += (size_t)ppw)
             {
@@ -623,11 +628,10 @@ struct ResidentSet
             if (d.bandW > 0 && d.bandW <= 32) sizeB += align4(4ll * d.la);
             if (d.bandW == 0)
             {
-                if (d.R > kMaxR)
-                    throw std::runtime_error("a pair whose shorter sequence exceeds " + std::to_string(32 * kMaxR) +
-                                             " nt has active edges on more than " + std::to_string(ctx.bandMaxW) +
-                                             " diagonals: outside the band kernels and the single-pass full-matrix kernel");
-                sizeB += align4(32ll * ((d.nSteps + 31) / 32)) + 32 + align4(32ll * d.nSteps * d.W);
+                // no usable band: the single-pass full-matrix kernel up to 640 nt, the row-by-row kernel beyond
+                d.dense = (d.R > kMaxR || (ctx.forceRows && ctx.dp.go < ctx.dp.ge)) ? 1 : 0;
+                if (d.dense) sizeB += align4(4ll * (d.la + 1)) + align4(((int64_t)(d.lb + 1) * (d.la + 1) + 3) / 4);
+                else sizeB += align4(32ll * ((d.nSteps + 31) / 32)) + 32 + align4(32ll * d.nSteps * d.W);
             }
         }
         for (size_t g = firstNewGroup; g < groups.size(); ++g)
@@ -658,6 +662,11 @@ struct ResidentSet
                     if (d.bandQ == 16) ++wk.stats.reserved[2];  // ... of those in blocks of 16 diagonals
                     wk.stats.reserved[3] += d.bandW;            // sum of their band widths
                 }
+            }
+            else if (d.dense)
+            {
+                d.offFlags = rB.take(4ll * (d.la + 1));                                     // S, V of two rows
+                d.offTrace = rB.take(((int64_t)(d.lb + 1) * (d.la + 1) + 3) / 4);           // one decision byte per cell
             }
             else
             {
@@ -701,7 +710,7 @@ struct ResidentSet
                 pilot->inters += d.D;
                 // scores + trace + closed-form records of the band, or stream + trace of the full-matrix kernel
                 pilot->dpBytes += d.bandW > 0 ? 4.6 * d.bandW * (d.lb + 1) + 16.0 * (d.la + d.lb + 2)
-                                              : 4.0 * d.nVals + 128.0 * d.nSteps * d.W;
+                                 : (d.dense ? 5.0 * (d.la + 1.0) * (d.lb + 1.0) : 4.0 * d.nVals + 128.0 * d.nSteps * d.W);
             }
             return;
         }
@@ -720,7 +729,7 @@ struct ResidentSet
             d.offInterCold = rC.take(4ll * d.D);
             wk.stats.n_active_edges += d.E; wk.stats.n_interactions += d.D;
             wk.stats.filter_cells += 2ll * d.la * d.lb;
-            if (d.bandW == 0) fullPairs[d.R].push_back(base + i);
+            if (d.bandW == 0) fullPairs[d.dense ? 0 : d.R].push_back(base + i);   // key 0: row-by-row kernel
             liveLanes16 += std::max(1, d.bandW / 32);
         }
         CK(cudaMemcpyAsync(dCd, cd, sizeof(PairDesc) * (size_t)n, cudaMemcpyHostToDevice, st));
@@ -807,7 +816,7 @@ struct ResidentSet
             for (BandLaunch const & b : bandLaunches)
                 std::fprintf(stderr, "[lara_b200]   DP class band G=%d Q=%d (W=%d): %d slots\n", b.G, b.Q, 2 * b.G * b.Q, b.nSlots);
             for (auto const & f : fullLaunches)
-                std::fprintf(stderr, "[lara_b200]   DP class full matrix R=%d: %d pairs\n", std::get<0>(f), std::get<2>(f));
+                std::fprintf(stderr, "[lara_b200]   DP class full matrix %s=%d: %d pairs\n", std::get<0>(f) ? "R" : "row by row, R", std::get<0>(f), std::get<2>(f));
         }
     }
 
@@ -853,8 +862,12 @@ struct ResidentSet
             for (size_t k = 0; k < fullLaunches.size(); ++k)
             {
                 CK(cudaStreamWaitEvent(wk.aux[k], wk.evFork, 0));
-                CK(launch_gotoh_fill(std::get<0>(fullLaunches[k]), std::get<2>(fullLaunches[k]), dTable + std::get<1>(fullLaunches[k]),
-                                     dDesc, dState, arena, dv.negBuf, dp.go, dp.ge, wk.aux[k]));
+                if (std::get<0>(fullLaunches[k]) == 0)
+                    CK(launch_gotoh_rows(std::get<2>(fullLaunches[k]), dTable + std::get<1>(fullLaunches[k]), dDesc, dState, arena,
+                                         dp.go, dp.ge, wk.aux[k]));
+                else
+                    CK(launch_gotoh_fill(std::get<0>(fullLaunches[k]), std::get<2>(fullLaunches[k]), dTable + std::get<1>(fullLaunches[k]),
+                                         dDesc, dState, arena, dv.negBuf, dp.go, dp.ge, wk.aux[k]));
                 CK(cudaEventRecord(wk.auxJoin[k], wk.aux[k]));
                 wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
             }
@@ -1229,12 +1242,14 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_BANDMAXW")) ctx->bandMaxW = std::max(0, std::min(1024, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BANDMINWARPS")) ctx->bandMinWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BAND24")) ctx->band24 = std::atoi(e) != 0;
+    if (char const * e = std::getenv("LARA_B200_BANDCLASSMINWARPS")) ctx->bandClassMinWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BAND24MINWARPS")) ctx->band24MinWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BANDQ")) ctx->bandForceQ = std::atoi(e);
     if (char const * e = std::getenv("LARA_B200_VERBOSE")) ctx->verbose = std::atoi(e);
     if (char const * e = std::getenv("LARA_B200_SMEMCAND")) ctx->postSmemCand = std::max(32, std::min(2048, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BATCHCAP")) ctx->batchPairsCap = (size_t)std::max(0, std::atoi(e));
+    if (char const * e = std::getenv("LARA_B200_ROWS")) ctx->forceRows = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_REFILL")) ctx->refillMode = std::max(0, std::min(2, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_WORKERPAIRS")) ctx->workerMinPairs = (size_t)std::max(1, std::atoi(e));
     ctx->P = *params;
@@ -1448,9 +1463,10 @@ int lara_gpu_prepare_pairs(lara_ctx * ctx, int64_t n_pairs, int32_t const * idx_
         op.request = p;
         if (op.la > 32767)
             return set_err(ctx, LARA_E_UNSUPPORTED, "sequences longer than 32,767 nt are not supported (16-bit positions)");
-        if ((op.lb + 31) / 32 > kMaxR && !(ctx->bandMode && ctx->dp.go < ctx->dp.ge))
+        if ((op.lb + 31) / 32 > kMaxR && !(ctx->dp.go < ctx->dp.ge))
             return set_err(ctx, LARA_E_UNSUPPORTED, "shorter sequence of a pair exceeds " + std::to_string(32 * kMaxR) +
-                                                     " nt (single-pass DP limit; the band kernels are switched off)");
+                                                     " nt and gap open >= gap extend: neither the band kernels nor the row-by-row "
+                                                     "kernel cover these gap costs");
     }
     {
         // the post kernel keeps the lines of a pair in shared memory (kernels_post.cu: WarpSmem)

@@ -59,7 +59,8 @@ struct PairDesc
     int32_t bitWords;           // words per row of the active bitmap: ceil(lb / 32)
     int32_t kCap;               // upper bound of matching candidates per iteration
     int32_t outIdx;             // position of the pair in the device's prepared pair list (== its result slot)
-    int32_t pad0_;
+    int32_t dense;              // 1: row-by-row full-matrix kernel (kernels_rows.cu): offVals = dense (lb+1) x (la+1) scores,
+                                //    offTrace = one decision byte per cell, offFlags = four rows of la + 1 ints (S, V buffers)
     int64_t offBits;            // active bitmap   [la][bitWords]
     int64_t offRowStart;        // first compact edge id of bitmap row a  [la + 1]
     int64_t offFlags;           // per lane step flags: bit (t & 31) of word [lane][t >> 5], nFlagWords words per lane
@@ -156,6 +157,9 @@ struct PairOutHdr
 // DP fill over the pairs listed in pairIdx[0..n) that all have the same R.
 cudaError_t launch_gotoh_fill(int R, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t const * negBuf, int32_t go, int32_t ge, cudaStream_t stream);
+// full-matrix DP fill, row by row, one block per pair of any size (kernels_rows.cu): pairs listed in pairIdx[0..n)
+cudaError_t launch_gotoh_rows(int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
+                              int32_t go, int32_t ge, cudaStream_t stream);
 // band DP fill (kernels_band.cu) over warp groups of 32 / G pairs with the same band shape (G lanes per pair, blocks
 // of Q diagonals): pairIdx[0..nSlots) lists the groups slot by slot, -1 = empty slot
 cudaError_t launch_gotoh_band(int G, int Q, int nSlots, int32_t const * pairIdx, PairDesc const * desc, PairState * state,

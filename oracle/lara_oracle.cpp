@@ -103,6 +103,10 @@ float generate_edges(uint8_t const * A, int la, uint8_t const * B, int lb, int32
 // Output: per alignment column (left to right) an op: 0 = match (A,B), 1 = gap in A (consumes B,
 // "vertical"), 2 = gap in B (consumes A, "horizontal").
 // ---------------------------------------------------------------------------------------------
+// developer statistics (LARA_ORACLE_STATS=1): largest |S| of an active cell and largest |score| seen by the DP
+static bool g_dbgRange = std::getenv("LARA_ORACLE_STATS") != nullptr;
+static int64_t g_dbgMaxS = 0, g_dbgMaxP = 0;
+
 ScoreType gotoh_fill(int la, int lb, ScoreType const * pssm, ScoreType go, ScoreType ge,
                      std::vector<uint8_t> & trace)
 {
@@ -152,6 +156,8 @@ ScoreType gotoh_fill(int la, int lb, ScoreType const * pssm, ScoreType go, Score
             if (d < g) { s = g; t = t2 | t; } else { s = d; t = T_DIAG | t; }
             S[r] = s; H[r] = h;
             tcol[r] = t;
+            if (g_dbgRange) { int64_t const a = std::llabs((long long)s); if (a > g_dbgMaxS && prow[r - 1] > DP_NEG) g_dbgMaxS = a;
+                              int64_t const b = std::llabs((long long)prow[r - 1]); if (prow[r - 1] > PSSM_INIT && b > g_dbgMaxP) g_dbgMaxP = b; }
         }
         lastV = V; lastH = H[lb];
     }
@@ -598,9 +604,9 @@ void solve_pair(lara_params const * P, SeqView const & sa, SeqView const & sb, i
     {
         double const it = (double)(P->num_iterations - (int32_t)remaining);
         std::fprintf(stderr, "[oracle] pair %d %d la %d lb %d E %zu D %lld iterations %.0f per iteration: lines %.1f with-interactions %.1f "
-                             "interactions-of-lines %.1f list %.1f candidates %.1f rescanned %.1f\n", idxFirst, idxSecond, lag.la, lag.lb,
+                             "interactions-of-lines %.1f list %.1f candidates %.1f rescanned %.1f max|S| %lld max|score| %lld\n", idxFirst, idxSecond, lag.la, lag.lb,
                      lag.cellOf.size(), (long long)lag.dimension(), it, lag.stLines / it, lag.stWork / it, lag.stItems / it,
-                     lag.stList / it, lag.stCand / it, lag.stRescan / it);
+                     lag.stList / it, lag.stCand / it, lag.stRescan / it, (long long)g_dbgMaxS, (long long)g_dbgMaxP);
     }
     // getStructureLines, src/lagrange.hpp:437-487
     bool swapIdx = idxFirst > idxSecond;

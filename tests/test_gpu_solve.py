@@ -83,6 +83,38 @@ def test_solve_long_sequences(built):
     assert st.reserved[1] == 3                      # all three pairs ran banded
 
 
+def test_solve_long_unequal_pair(built):
+    """A pair whose shorter sequence exceeds the single-pass full-matrix kernel (640 nt) and whose active edges span more
+    diagonals than the widest band (1,024): 2,100 x 680 nt runs on the row-by-row kernel; its neighbours in the same
+    call take bands."""
+    import lara_b200 as lb
+    rng = np.random.default_rng(44)
+    s = lb.InputStorage()
+    for name, L in (("long", 2100), ("mid", 680), ("short", 660)):
+        seq = "".join("ACGU"[i] for i in rng.integers(0, 4, size=L))
+        pairs = []
+        used = set()
+        for _ in range(L // 6):
+            i, j = sorted(int(x) for x in rng.integers(0, L, size=2))
+            if j - i < 4 or i in used or j in used:
+                continue
+            used.add(i); used.add(j)
+            pairs.append((i, j, float(rng.uniform(1.0, 5.5))))
+        s.add_record(name, seq, pairs)
+    s.finish()
+    got, want = _solve_store(s, num_iterations=10, max_nondecreasing=3)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+
+
+def test_solve_negative_step(built):
+    """SIMD-build arithmetic on skewed lengths for many iterations: the wrapping int32 product makes negative steps, so
+    multipliers of +1 entries go up and those of -1 entries go down (every touched row is rescanned or raised by what
+    its multiplier really did)."""
+    files = util.make_input(seed=45, n=16, length=0, skew=True)
+    got, want, _ = _solve_both(files, num_iterations=220, max_nondecreasing=10, step_mode=1)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+
+
 def test_solve_skewed_lengths(built):
     """Lognormal lengths 50..600 (BASELINE config C5): mixed band widths and launch classes in one batch."""
     files = util.make_input(seed=38, n=14, length=0, skew=True)
@@ -99,6 +131,8 @@ def test_solve_skewed_lengths(built):
     dict(LARA_B200_BANDMAXW="32", LARA_B200_BATCH="33"),
     dict(LARA_B200_BANDMINWARPS="1"),                   # lets the 24-diagonal one-thread shape in on a small batch
     dict(LARA_B200_BAND24="0", LARA_B200_BANDMINWARPS="1"),
+    dict(LARA_B200_BAND="0", LARA_B200_ROWS="1"),       # row-by-row full-matrix kernel (the fallback for pairs of any size)
+    dict(LARA_B200_BANDMAXW="32", LARA_B200_ROWS="1", LARA_B200_FUSED="0"),
     dict(LARA_B200_BANDMINWARPS="100000"),              # low-latency form: blocks of 8 diagonals, twice the lanes per pair
     dict(LARA_B200_BANDMINWARPS="1", LARA_B200_BATCHCAP="16", LARA_B200_REFILL="2"),   # 16 slots refilled as pairs finish
 ])

@@ -17,11 +17,7 @@ except Exception as e:
 PY
 }
 run c3 "" "--steps 2 --warmup 1 $B"
-run c3_unfused "LARA_B200_FUSED=0" "--steps 2 --warmup 1 $B"
-run c3_w1 "LARA_B200_WORKERS=1" "--steps 1 --warmup 1 $B"
+run c3_cls1 "LARA_B200_BANDCLASSMINWARPS=1" "--steps 2 --warmup 1 $B"
 run ew8 "" "--steps 2 --warmup 1 --emulate-world 8 $B"
-run ew8_mw100 "LARA_B200_BANDMINWARPS=100" "--steps 2 --warmup 1 --emulate-world 8 $B"
-run ew8_w1_mw100 "LARA_B200_WORKERS=1 LARA_B200_BANDMINWARPS=100" "--steps 2 --warmup 1 --emulate-world 8 $B"
+run ew8_w1 "LARA_B200_WORKERS=1" "--steps 2 --warmup 1 --emulate-world 8 $B"
 run ew4 "" "--steps 2 --warmup 1 --emulate-world 4 $B"
-run ew4_mw100 "LARA_B200_BANDMINWARPS=100" "--steps 2 --warmup 1 --emulate-world 4 $B"
-timeout 900 python tools/gpu_check.py c5 120 step_mode=1 > gpurun_out/${TAG}_c5simd.txt 2>&1; tail -12 gpurun_out/${TAG}_c5simd.txt
