@@ -602,8 +602,9 @@ cudaError_t launch_gotoh_band_multi(int nClasses, BandLaunch const * cls, int32_
         if (cls[k].nSlots <= 0) continue;
         if (tab.n >= kMaxBandClasses || !band_shape_supported(cls[k].G, cls[k].Q)) return cudaErrorInvalidValue;
         int const slotsPerBlock = 4 * (32 / cls[k].G);
-        // LARA_B200_FUSED=0: the one-thread-per-pair shapes run the generic body (measurement switch, same results)
-        static bool const fused = []() { char const * e = std::getenv("LARA_B200_FUSED"); return !e || std::atoi(e) != 0; }();
+        // LARA_B200_FUSED=1: the one-thread-per-pair shapes run the two-rows-at-a-time body (same results; measured no
+        // faster on B200: profiles/README.md r2, so the generic body with its lower register count is the default)
+        static bool const fused = []() { char const * e = std::getenv("LARA_B200_FUSED"); return e && std::atoi(e) != 0; }();
         tab.shape[tab.n] = (cls[k].G << 8) | cls[k].Q | ((fused && cls[k].G == 1) ? 0x10000 : 0);
         anyOne = anyOne || (fused && cls[k].G == 1);
         tab.firstBlock[tab.n] = blocks;

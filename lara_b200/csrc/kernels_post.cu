@@ -85,6 +85,7 @@ struct WarpSmem
     int32_t * curE;         // [maxLb]  compact edge id of the k-th line that has interactions (alignment order)
     int16_t * workLine;     // [maxLb]  ... and its line index
     uint8_t * matched;      // [maxLb]
+    uint8_t * seqB;         // [512]    Rna5 codes of the second sequence, in the upper half of win (free until step 3)
     unsigned long long * cand;  // [smemCand]
     int32_t * misc;         // [32]: 0 nList, 1 nCand, 2 matchScore, 3..10 selection weights, 11 error, 16..23 selection
     uint32_t * win;         // [256] traceback window (full mode: 32 rows x 32 nibbles; band mode: 8 word rows x L)
@@ -383,8 +384,9 @@ __device__ void band_end_values(BandView const & v, int32_t & sE, int32_t & vE, 
 
 // Traceback + evaluateLines for band mode: the segment walker of traceback_walk over a polymorphic cell fetch.
 // Window = 32 rows x 32 band diagonals around the walker, in shared memory as four decision planes per row: lane i
-// fetches row rHi - i (the trace units of kernels_band.cu are bit planes already) and writes win[4 i + k] = plane k of
-// that row, window diagonal x at bit x.  The walk asks for one decision of a cell at a time.
+// fetches row rHi - i (the trace units of kernels_band.cu are bit planes already) and assembles plane k of
+// that row, window diagonal x at bit x, stored plane by plane (win[32 k + i]).  The walk asks for one decision of a
+// cell at a time.
 __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, int32_t hEnd, uint32_t * linesRev,
                               uint32_t * win, int32_t & gapOut, int lane)
 {
@@ -462,7 +464,9 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
                     }
                 }
             }
-            *reinterpret_cast<uint4 *>(win + 4 * lane) = make_uint4(w[0], w[1], w[2], w[3]);
+            // plane-major: the 32 lanes of a diagonal or vertical look-up read 32 neighbouring words (no bank conflicts)
+            #pragma unroll
+            for (int k = 0; k < 4; ++k) win[32 * k + lane] = w[k];
         }
         __syncwarp();
         // One decision (bit `plane` of the trace nibble) of cell (ci, ri).
@@ -482,7 +486,7 @@ __device__ int traceback_band(BandView const & v, int32_t sEnd, int32_t vEnd, in
             int const x = dd - v.dLo - xLo, row = rHi - ri;
             if (row > 31 || x < 0 || x > 31) return 0u;
             known = true;
-            return (win[4 * row + plane] >> x) & 1u;
+            return (win[32 * plane + row] >> x) & 1u;
         };
         for (;;)
         {
@@ -695,8 +699,10 @@ __device__ int32_t greedy_matching(unsigned long long const * keys, int K, int l
     return warp_sum(score);
 }
 
-__device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b, bool & hasInter)
+__device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b, bool & hasInter,
+                                       int & codeA)
 {
+    codeA = -1;                                 // without a row record: read the sequence
     hasInter = true;                            // without a row record: unknown, the edge record tells
     if (d.offRowRec)
     {
@@ -704,6 +710,7 @@ __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __res
         // word of the cells that have interactions
         int4 const rec = __ldg(reinterpret_cast<int4 const *>(arena + d.offRowRec) + a);
         int const k = b - (a - d.dHi);
+        codeA = rec.w;
         if (k < 0 || k > 31 || !(((uint32_t)rec.y >> k) & 1u)) return -1;
         hasInter = ((uint32_t)rec.z >> k) & 1u;
         return rec.x + __popc((uint32_t)rec.y & ((1u << k) - 1u));
@@ -721,7 +728,8 @@ __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __res
 __device__ __forceinline__ int edge_of(PairDesc const & d, int32_t const * __restrict__ arena, int a, int b)
 {
     bool h;
-    return edge_of(d, arena, a, b, h);
+    int c;
+    return edge_of(d, arena, a, b, h, c);
 }
 
 // 80 registers (6 x 128 threads): with one-warp blocks 24 pairs per SM.  More pairs per SM (72 or 64 registers, or
@@ -756,9 +764,18 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
     sm.lineOfA = (int16_t *)base;                             base += ((size_t)maxLa * 2 + 15) / 16 * 16;
     sm.workLine = (int16_t *)base;                            base += ((size_t)maxLb * 2 + 15) / 16 * 16;
     sm.matched = (uint8_t *)base;
+    sm.seqB = (uint8_t *)(sm.win + 128);
 
     int const la = d.la, lb = d.lb;
     (void)lb;
+    // bases of the second sequence for the sequence scores of step 2 (the row records carry those of the first); no
+    // shared memory of their own: one more KB per warp costs the kernel its L1
+    bool const stagedB = d.offRowRec != 0 && d.lb <= 512;
+    if (stagedB)
+    {
+        uint8_t const * __restrict__ sb = in.seqCat + in.seqOff[d.seqSecond];
+        for (int i = lane; i < d.lb; i += 32) sm.seqB[i] = sb[i];
+    }
     if (d.offRowRec && !(tune & 4))
     {
         // the row records of the edge lookup (step 2; 16 bytes per row): into L2 while the traceback runs
@@ -846,10 +863,16 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
                 uint32_t const ab = sm.linesRev[nLines - 1 - i];
                 int const a = (int)(ab >> 16), b = (int)(ab & 0xffffu);
                 sm.lineOfA[a] = (int16_t)i;
-                e = edge_of(d, arena, a, b, work);
+                int codeA;
+                e = edge_of(d, arena, a, b, work, codeA);
                 if (e < 0) { sm.misc[11] = 1; work = false; }   // "Alignment match where no alignment edge is defined!"
                 else if (!work)
-                    lbSeq += __float2int_rz(__fmul_rn(scale, __int2float_rn(P.tab[(int)seqA[a] * 5 + (int)seqB[b]])));
+                {
+                    // the row record carries the base of A, the bases of B were staged when the kernel started
+                    int const ca = codeA >= 0 ? codeA : (int)seqA[a];
+                    int const cb = stagedB ? (int)sm.seqB[b] : (int)seqB[b];
+                    lbSeq += __float2int_rz(__fmul_rn(scale, __int2float_rn(P.tab[ca * 5 + cb])));
+                }
                 sm.matched[i] = 0;
             }
             unsigned const bal = __ballot_sync(kFull, work);

@@ -277,8 +277,8 @@ setup_count_kernel(int n, PairDesc * __restrict__ desc, PairState * __restrict__
                 uint32_t word = 0u;
                 if (lo >= 0) word = strip_bits(bits + (size_t)a * bitWords, bitWords, lo, 32);
                 else if (lo > -32) word = strip_bits(bits + (size_t)a * bitWords, bitWords, 0, 32) << (-lo);
-                // third word: the cells that have interactions, set by setup_fill_kernel
-                reinterpret_cast<int4 *>(arena + d.offRowRec)[a] = make_int4(carry + ex, (int)word, 0, 0);
+                // third word: the cells that have interactions, set by setup_fill_kernel; fourth: the base of A
+                reinterpret_cast<int4 *>(arena + d.offRowRec)[a] = make_int4(carry + ex, (int)word, 0, (int)A[a]);
             }
         }
         carry += total;

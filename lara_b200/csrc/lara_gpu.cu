@@ -135,6 +135,9 @@ struct lara_ctx
     bool prepared = false, ran = false;
     lara_stats stats{};
     size_t batchPairsCap = 0;               // test hook: max pairs per batch, 0 = automatic (env LARA_B200_BATCHCAP)
+    bool postInOrder = true;                // post kernel over the pairs in admission order instead of slot order (env LARA_B200_POSTORDER=0: slot order)
+    bool splitLaunch = false;               // env LARA_B200_SPLIT=1: band classes of >= bandSplitWarps warps (except the largest)
+    int bandSplitWarps = 256;               // run as launches of their own (LARA_B200_SPLITWARPS)
     bool forceRows = false;                 // every pair without a band runs the row-by-row kernel (env LARA_B200_ROWS=1; tests)
     int refillMode = 1;                     // slot refill: 0 = set by set, 1 = as slots free up while the queue is long,
                                             // 2 = always as slots free up (env LARA_B200_REFILL)
@@ -356,10 +359,12 @@ struct ResidentSet
     int live = 0;
     int64_t liveLanes16 = 0;                    // lanes of the live pairs' fill with blocks of 16 diagonals
     bool have24 = false;
+    bool slabFree = true;                       // no live pair has arrays in the worker's slab: the next cohort may take it
     // slot table on the device and its launch geometry
     int32_t * dTable = nullptr;
     size_t tableCap = 0;
-    int nSlots = 0;
+    size_t nBigClasses = 0;                     // band classes with a launch of their own: bandLaunches[0 .. nBigClasses)
+    int nSlots = 0, nPost = 0;                  // slots of the DP classes; pairs of the post kernel (listed after the slots)
     std::vector<BandLaunch> bandLaunches;
     std::vector<std::tuple<int, int, int>> fullLaunches;        // R, offset, count
     int maxLa = 1, maxLb = 1, smemCand = 32;
@@ -407,8 +412,8 @@ struct ResidentSet
         int const n = (int)(end - begin);
         int const base = (int)desc.size();
         if ((size_t)base + (size_t)n > pairCap) throw std::runtime_error("resident set: pair arrays too small");
-        bool const useSlab = slabHintBytes > 0 && cohorts.empty() && !pilot;
-        if (useSlab && (double)wk.slabInts * 4 < slabHintBytes)
+        bool const useSlab = slabHintBytes > 0 && slabFree && !pilot;
+        if (useSlab && cohorts.empty() && (double)wk.slabInts * 4 < slabHintBytes)
         {
             CK(cudaStreamSynchronize(s));
             CK(cudaFree(wk.slab));
@@ -418,6 +423,7 @@ struct ResidentSet
             wk.slabInts = want;
         }
         if (cohorts.empty() && !pilot) arena = wk.slab ? wk.slab : reinterpret_cast<int32_t *>(dDesc);
+        if (useSlab) slabFree = false;
         cohorts.emplace_back();
         Cohort * co = &cohorts.back();
         co->base = base; co->n = n;
@@ -755,6 +761,28 @@ struct ResidentSet
                          reused, groups.size() - firstNewGroup, live);
     }
 
+    // Every pair of the set has finished: forget its groups, so that the next cohort starts from the worker's slab like
+    // the first one did (no pair's arrays are in use any more; st: the stream the next set-up will run on).
+    void begin_new_set(cudaStream_t st)
+    {
+        for (Cohort & c : cohorts)
+        {
+            for (void * f : c.pooled) CK(cudaFreeAsync(f, s));
+            c.pooled.clear();
+        }
+        for (void * f : keep) CK(cudaFreeAsync(f, s));
+        keep.clear();
+        groups.clear();
+        for (int32_t & g : groupOf) g = -1;
+        fullPairs.clear();
+        have24 = false;
+        liveLanes16 = 0;
+        slabFree = true;
+        // the set-up kernels of the next cohort write into the slab: after everything queued on the worker's stream
+        CK(cudaEventRecord(evSide, s));
+        CK(cudaStreamWaitEvent(st, evSide, 0));
+    }
+
     // ---- slot table: the occupied groups class by class (most slots first), then the full-matrix classes -----------
     void rebuild_table()
     {
@@ -774,6 +802,15 @@ struct ResidentSet
                 table.insert(table.end(), groups[(size_t)g].occ.begin(), groups[(size_t)g].occ.end());
             bandLaunches.push_back(BandLaunch{G, Q, (int)table.size() - off, off});
         }
+        {
+            // classes (other than the largest) that fill a good part of the machine by themselves come first: they get
+            // launches of their own (enqueue_step)
+            nBigClasses = 0;
+            for (size_t k = 1; k < bandLaunches.size(); ++k)
+                if ((int64_t)bandLaunches[k].nSlots * bandLaunches[k].G / 32 >= ctx.bandSplitWarps)
+                    std::swap(bandLaunches[nBigClasses++], bandLaunches[k]);
+            // (the swap moved the largest class behind the big ones when there are any; order inside the rest does not matter)
+        }
         for (auto & kv : fullPairs)
         {
             std::vector<int32_t> & v = kv.second;
@@ -783,6 +820,15 @@ struct ResidentSet
             table.insert(table.end(), v.begin(), v.end());
         }
         nSlots = (int)table.size();
+        // the post kernel takes the pairs in admission order (== the order of their arrays in memory), one warp each
+        {
+            std::vector<int32_t> inOrder;
+            inOrder.reserve(table.size());
+            for (int32_t p : table) if (p >= 0) inOrder.push_back(p);
+            std::sort(inOrder.begin(), inOrder.end());
+            nPost = (int)inOrder.size();
+            table.insert(table.end(), inOrder.begin(), inOrder.end());
+        }
         if (table.size() > tableCap)
         {
             if (dTable) CK(cudaFreeAsync(dTable, s));
@@ -848,10 +894,14 @@ struct ResidentSet
         DevParams const & dp = ctx.dp;
         CK(cudaEventRecord(e0, s));
         // full-matrix classes (pairs without a usable band) on side streams, all band classes in one launch
-        if (!fullLaunches.empty())
+        // (LARA_B200_SPLIT=1: classes that fill a good part of the machine on their own run as launches of their own beside
+        // it; measured on C3 within 1-2 % of the single launch, either way, from box to box: off)
+        size_t const nSplit = ctx.splitLaunch ? nBigClasses : 0;
+        size_t const nSide = fullLaunches.size() + nSplit;
+        if (nSide)
         {
             if (!wk.evFork) CK(cudaEventCreateWithFlags(&wk.evFork, cudaEventDisableTiming));
-            while (wk.aux.size() < fullLaunches.size())
+            while (wk.aux.size() < nSide)
             {
                 cudaStream_t st; cudaEvent_t ev;
                 CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
@@ -871,16 +921,30 @@ struct ResidentSet
                 CK(cudaEventRecord(wk.auxJoin[k], wk.aux[k]));
                 wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
             }
+            for (size_t k = 0; k < nSplit; ++k)
+            {
+                size_t const a = fullLaunches.size() + k;
+                CK(cudaStreamWaitEvent(wk.aux[a], wk.evFork, 0));
+                CK(launch_gotoh_band_multi(1, &bandLaunches[k], dTable, dDesc, dState, arena, dp.go, dp.ge, wk.aux[a]));
+                CK(cudaEventRecord(wk.auxJoin[a], wk.aux[a]));
+                wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
+            }
         }
         if (!bandLaunches.empty())
         {
-            CK(launch_gotoh_band_multi((int)bandLaunches.size(), bandLaunches.data(), dTable, dDesc, dState, arena, dp.go, dp.ge, s));
+            // bandLaunches: the nBigClasses classes with launches of their own first, then the largest class and the small ones
+            CK(launch_gotoh_band_multi((int)(bandLaunches.size() - nSplit), bandLaunches.data() + nSplit, dTable, dDesc, dState, arena,
+                                       dp.go, dp.ge, s));
             wk.stats.kernel_launches += 1; wk.stats.dp_launches += 1;
         }
-        for (size_t k = 0; k < fullLaunches.size(); ++k) CK(cudaStreamWaitEvent(s, wk.auxJoin[k], 0));
+        for (size_t k = 0; k < nSide; ++k) CK(cudaStreamWaitEvent(s, wk.auxJoin[k], 0));
         CK(cudaEventRecord(e1, s));
-        CK(launch_iterate_post(nSlots, dTable, dDesc, dState, arena, dp, dv.dOutHdr, dv.dOutLines, dv.dOutOff, dFinished,
-                               maxLa, maxLb, smemCand, dv.in, s));
+        if (ctx.postInOrder)
+            CK(launch_iterate_post(nPost, dTable + nSlots, dDesc, dState, arena, dp, dv.dOutHdr, dv.dOutLines, dv.dOutOff, dFinished,
+                                   maxLa, maxLb, smemCand, dv.in, s));
+        else
+            CK(launch_iterate_post(nSlots, dTable, dDesc, dState, arena, dp, dv.dOutHdr, dv.dOutLines, dv.dOutOff, dFinished,
+                                   maxLa, maxLb, smemCand, dv.in, s));
         wk.stats.kernel_launches += 1;
         CK(cudaEventRecord(e2, s));
         wk.stats.reserved[7] += 1;
@@ -1039,7 +1103,14 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
                         if (e2 > b2)
                         {
                             // the slots are known to be free: their pairs were reported by a block that has completed
-                            rs.admit(b2, e2, rs.side, 0);
+                            double bytes2 = 0;
+                            if (rs.live == 0)
+                            {
+                                // a drained set: the next one is laid out in the slab like the first
+                                rs.begin_new_set(rs.side);
+                                bytes2 = (double)wk.slabInts * 4;       // what does not fit the slab comes from the pool
+                            }
+                            rs.admit(b2, e2, rs.side, bytes2);
                             CK(cudaEventRecord(rs.evSide, rs.side));
                             pendingSplice = true;
                         }
@@ -1050,7 +1121,7 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
                 if (rs.live == 0 && !pendingSplice && !more)
                 {
                     // every pair is accounted for; the block just queued finds nothing to do
-                    read_block(outstanding);
+                    if (outstanding >= 0) read_block(outstanding);
                     break;
                 }
                 if (steps > maxSteps) throw std::runtime_error("pairs did not finish within the iteration limit");
@@ -1249,6 +1320,9 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_SMEMCAND")) ctx->postSmemCand = std::max(32, std::min(2048, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_BATCH")) ctx->batchPairsDefault = (size_t)std::max(32, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_BATCHCAP")) ctx->batchPairsCap = (size_t)std::max(0, std::atoi(e));
+    if (char const * e = std::getenv("LARA_B200_POSTORDER")) ctx->postInOrder = std::atoi(e) != 0;
+    if (char const * e = std::getenv("LARA_B200_SPLIT")) ctx->splitLaunch = std::atoi(e) != 0;
+    if (char const * e = std::getenv("LARA_B200_SPLITWARPS")) ctx->bandSplitWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_ROWS")) ctx->forceRows = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_REFILL")) ctx->refillMode = std::max(0, std::min(2, std::atoi(e)));
     if (char const * e = std::getenv("LARA_B200_WORKERPAIRS")) ctx->workerMinPairs = (size_t)std::max(1, std::atoi(e));

@@ -84,7 +84,8 @@ struct PairDesc
     int64_t offInter;           // per interaction, 16 bytes (hot): { reverse index, partner cell, structScore, dual }  [D]
     int64_t offInterCold;       // per interaction, 16 bytes (cold): { partner edge, seqScore of the partner, owner edge, 0 }  [D]
     int64_t offRowRec;          // bands of <= 32 diagonals, per row a of the bitmap, 16 bytes: { id of the row's first edge,
-                                //   activity bits of b = a - dHi .. a - dHi + 31, of those the cells with interactions, 0 }   [la]   (0: not present)
+                                //   activity bits of b = a - dHi .. a - dHi + 31, of those the cells with interactions,
+                                //   Rna5 code of A[a] }   [la]   (0: not present)
     int64_t offLines;           // current lines  (a << 16) | b  [lb]
     int64_t offBest;            // best lines     (a << 16) | b | matched << 31  [lb]
     int64_t offCand;            // global candidate buffer for the matching sort, 2 words each [2 * kCap] (8-byte aligned)

@@ -132,7 +132,9 @@ def test_solve_skewed_lengths(built):
     dict(LARA_B200_BANDMINWARPS="1"),                   # lets the 24-diagonal one-thread shape in on a small batch
     dict(LARA_B200_BAND24="0", LARA_B200_BANDMINWARPS="1"),
     dict(LARA_B200_BAND="0", LARA_B200_ROWS="1"),       # row-by-row full-matrix kernel (the fallback for pairs of any size)
-    dict(LARA_B200_BANDMAXW="32", LARA_B200_ROWS="1", LARA_B200_FUSED="0"),
+    dict(LARA_B200_BANDMAXW="32", LARA_B200_ROWS="1", LARA_B200_FUSED="1"),
+    dict(LARA_B200_SPLIT="1", LARA_B200_SPLITWARPS="1", LARA_B200_BANDMINWARPS="1", LARA_B200_BANDCLASSMINWARPS="1"),   # every class its own launch
+    dict(LARA_B200_FUSED="1", LARA_B200_BANDMINWARPS="1", LARA_B200_BANDCLASSMINWARPS="1"),        # two-rows-at-a-time body
     dict(LARA_B200_BANDMINWARPS="100000"),              # low-latency form: blocks of 8 diagonals, twice the lanes per pair
     dict(LARA_B200_BANDMINWARPS="1", LARA_B200_BATCHCAP="16", LARA_B200_REFILL="2"),   # 16 slots refilled as pairs finish
 ])

@@ -16,8 +16,6 @@ except Exception as e:
     print("[$1] no result", e)
 PY
 }
-run c3 "" "--steps 2 --warmup 1 $B"
-run c3_cls1 "LARA_B200_BANDCLASSMINWARPS=1" "--steps 2 --warmup 1 $B"
+run c3 "" "--steps 3 --warmup 1 $B"
 run ew8 "" "--steps 2 --warmup 1 --emulate-world 8 $B"
 run ew8_w1 "LARA_B200_WORKERS=1" "--steps 2 --warmup 1 --emulate-world 8 $B"
-run ew4 "" "--steps 2 --warmup 1 --emulate-world 4 $B"
