@@ -35,10 +35,21 @@ __device__ __forceinline__ long long warp_incl_max(long long v, int lane)
     return v;
 }
 
+// kMode 0: affine gap costs with go <= ge (the recursion above).
+// kMode 1: linear gap costs: the scalar reference hands gap open == gap extend to SeqAn's Needleman-Wunsch
+//          (SeqAn:align/global_alignment_unbanded.h:775-778, recursion dp_formula_linear.h:62-99): one matrix,
+//          S(c) = max(D(c), V(c), S(c-1) + g) with V(c) = S(c, r-1) + g; vertical wins the tie against horizontal, the
+//          diagonal the tie against the better gap; no end-cell correction; the traceback moves one cell at a time.
+// kMode 2: affine gap costs with go > ge (opening cheaper than extending): S >= V, H makes every gap cell an opening,
+//          V(c) = S(c, r-1) + go, H(c) = S(c-1) + go: the values and tie rules of mode 1 with g = go, every "opened" bit
+//          set, plus the affine end-cell correction (S, V, H of the end cell are reported).
+// In modes 1 and 2 the row is S(c) = c g + max_{k <= c} (max(D(k), V(k)) - k g): the same scan.
+template <int kMode>
 __global__ void __launch_bounds__(kRowsThreads)
 gotoh_rows_kernel(int n, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc,
                   PairState * __restrict__ state, int32_t * __restrict__ arena, int32_t go, int32_t ge)
 {
+    int32_t const gl = go;                          // modes 1, 2: cost of every gap position
     __shared__ long long sIncl[kRowsThreads];       // inclusive prefix maximum of g over the threads' runs
     __shared__ long long sExLast[kRowsThreads];     // maximum of g over a thread's run without its last column
     __shared__ long long sLastG[kRowsThreads];      // g of a thread's last column
@@ -58,7 +69,7 @@ gotoh_rows_kernel(int n, int32_t const * __restrict__ pairIdx, PairDesc const * 
     // row 0 (dp_formula_affine.h:245-281): S(c,0) = go + (c-1) ge, V = -inf; origin S = 0
     for (int c = c0; c < c1; ++c)
     {
-        buf[c] = c == 0 ? 0 : go + (c - 1) * ge;
+        buf[c] = c == 0 ? 0 : (kMode == 0 ? go + (c - 1) * ge : c * gl);
         buf[2 * ncol + c] = kDpNeg;
     }
     __syncthreads();
@@ -69,20 +80,31 @@ gotoh_rows_kernel(int n, int32_t const * __restrict__ pairIdx, PairDesc const * 
         int32_t * __restrict__ Sc = buf + (r & 1) * ncol;
         int32_t * __restrict__ Vc = buf + 2 * ncol + (r & 1) * ncol;
         int32_t const * __restrict__ sub = vals + (size_t)r * ncol;
-        int32_t const s0 = go + (r - 1) * ge;                   // column 0 (dp_formula_affine.h:291-325): S = V, H = -inf
+        int32_t const s0 = kMode == 0 ? go + (r - 1) * ge : r * gl;     // column 0 (dp_formula_affine.h:291-325): S = V, H = -inf
         // ---- pass 1: g(k) = m(k) - k ge of the thread's columns -> maximum, maximum without the last column, last
         long long runMax = kNoneG, exLast = kNoneG, lastG = kNoneG;
         for (int c = c0; c < c1; ++c)
         {
-            int32_t m;
-            if (c == 0) m = s0 + go;
+            long long g;
+            if (kMode == 0)
+            {
+                int32_t m;
+                if (c == 0) m = s0 + go;
+                else
+                {
+                    int32_t const dd = Sp[c - 1] + sub[c];
+                    int32_t const v = max(Vp[c] + ge, Sp[c] + go);
+                    m = max(dd, v) + go;
+                }
+                g = (long long)m - (long long)c * ge;
+            }
             else
             {
-                int32_t const dd = Sp[c - 1] + sub[c];
-                int32_t const v = max(Vp[c] + ge, Sp[c] + go);
-                m = max(dd, v) + go;
+                int32_t x;
+                if (c == 0) x = s0;
+                else x = max(Sp[c - 1] + sub[c], Sp[c] + gl);
+                g = (long long)x - (long long)c * gl;
             }
-            long long const g = (long long)m - (long long)c * ge;
             exLast = runMax;
             runMax = max(runMax, g);
             lastG = g;
@@ -116,28 +138,40 @@ gotoh_rows_kernel(int n, int32_t const * __restrict__ pairIdx, PairDesc const * 
             {
                 Sc[0] = s0; Vc[0] = s0;
                 trace[(size_t)r * ncol] = 0;
-                Pm1 = kNoneG; gPrev = (long long)(s0 + go); P = gPrev;           // P(1) = g(0)
+                Pm1 = kNoneG; gPrev = kMode == 0 ? (long long)(s0 + go) : (long long)s0; P = gPrev;     // P(1) = g(0)
                 continue;
             }
             int32_t const dd = Sp[c - 1] + sub[c];
-            int32_t const ve = Vp[c] + ge, vo = Sp[c] + go;
-            int32_t const v = max(ve, vo);
-            int32_t const h = (int32_t)((long long)(c - 1) * ge + P);
+            int32_t v, h;
+            uint32_t nib = 0u;
+            if (kMode == 0)
+            {
+                int32_t const ve = Vp[c] + ge, vo = Sp[c] + go;
+                v = max(ve, vo);
+                h = (int32_t)((long long)(c - 1) * ge + P);
+                if (ve < vo) nib |= kTrVOpen;           // V opened   (extension wins ties)
+                if (Pm1 < gPrev) nib |= kTrHOpen;       // H opened   (extension wins ties): H(c-1) + ge < m(c-1)
+            }
+            else
+            {
+                v = Sp[c] + gl;
+                h = (int32_t)((long long)c * gl + P);   // S(c-1) + g
+                nib = kTrVOpen | kTrHOpen;              // every gap cell stands alone: the walk takes one step at a time
+            }
             int32_t const mx = max(dd, v);
             int32_t const s = max(mx, h);
-            uint32_t nib = 0u;
             if (dd < s) nib |= kTrGap;                  // S from gap (diagonal wins ties)
             if (v < h) nib |= kTrFromH;                 // gap from H (vertical wins ties)
-            if (ve < vo) nib |= kTrVOpen;               // V opened   (extension wins ties)
-            if (Pm1 < gPrev) nib |= kTrHOpen;           // H opened   (extension wins ties): H(c-1) + ge < m(c-1)
             Sc[c] = s; Vc[c] = v;
             trace[(size_t)r * ncol + c] = (uint8_t)nib;
             if (r == lb && c == la)
             {
                 PairState & st = state[p];
-                st.currentUpper = s; st.sEnd = s; st.vEnd = v; st.hEnd = h;
+                st.currentUpper = s; st.sEnd = s;
+                // linear gap costs: SeqAn corrects nothing at the end cell (values that never equal S)
+                st.vEnd = kMode == 1 ? s - 1 : v; st.hEnd = kMode == 1 ? s - 1 : h;
             }
-            long long const g = (long long)(mx + go) - (long long)c * ge;
+            long long const g = kMode == 0 ? (long long)(mx + go) - (long long)c * ge : (long long)mx - (long long)c * gl;
             Pm1 = P; gPrev = g; P = max(P, g);
         }
         __syncthreads();
@@ -146,11 +180,13 @@ gotoh_rows_kernel(int n, int32_t const * __restrict__ pairIdx, PairDesc const * 
 
 } // namespace
 
-cudaError_t launch_gotoh_rows(int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
+cudaError_t launch_gotoh_rows(int mode, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
                               int32_t go, int32_t ge, cudaStream_t stream)
 {
     if (n <= 0) return cudaSuccess;
-    gotoh_rows_kernel<<<n, kRowsThreads, 0, stream>>>(n, pairIdx, desc, state, arena, go, ge);
+    if (mode == 0) gotoh_rows_kernel<0><<<n, kRowsThreads, 0, stream>>>(n, pairIdx, desc, state, arena, go, ge);
+    else if (mode == 1) gotoh_rows_kernel<1><<<n, kRowsThreads, 0, stream>>>(n, pairIdx, desc, state, arena, go, ge);
+    else gotoh_rows_kernel<2><<<n, kRowsThreads, 0, stream>>>(n, pairIdx, desc, state, arena, go, ge);
     return cudaGetLastError();
 }
 

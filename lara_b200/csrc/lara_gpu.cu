@@ -138,6 +138,8 @@ struct lara_ctx
     bool postInOrder = true;                // post kernel over the pairs in admission order instead of slot order (env LARA_B200_POSTORDER=0: slot order)
     bool splitLaunch = false;               // env LARA_B200_SPLIT=1: band classes of >= bandSplitWarps warps (except the largest)
     int bandSplitWarps = 256;               // run as launches of their own (LARA_B200_SPLITWARPS)
+    int rowsMode = 0;                       // form of the row-by-row kernel (kernels_rows.cu): 0 affine go <= ge, 1 linear gap
+                                            // costs (gap open == gap extend in the scalar build's arithmetic), 2 affine go > ge
     bool forceRows = false;                 // every pair without a band runs the row-by-row kernel (env LARA_B200_ROWS=1; tests)
     int refillMode = 1;                     // slot refill: 0 = set by set, 1 = as slots free up while the queue is long,
                                             // 2 = always as slots free up (env LARA_B200_REFILL)
@@ -635,7 +637,7 @@ struct ResidentSet
             if (d.bandW == 0)
             {
                 // no usable band: the single-pass full-matrix kernel up to 640 nt, the row-by-row kernel beyond
-                d.dense = (d.R > kMaxR || (ctx.forceRows && ctx.dp.go < ctx.dp.ge)) ? 1 : 0;
+                d.dense = (d.R > kMaxR || ctx.forceRows || ctx.rowsMode == 1) ? 1 : 0;
                 if (d.dense) sizeB += align4(4ll * (d.la + 1)) + align4(((int64_t)(d.lb + 1) * (d.la + 1) + 3) / 4);
                 else sizeB += align4(32ll * ((d.nSteps + 31) / 32)) + 32 + align4(32ll * d.nSteps * d.W);
             }
@@ -913,7 +915,7 @@ struct ResidentSet
             {
                 CK(cudaStreamWaitEvent(wk.aux[k], wk.evFork, 0));
                 if (std::get<0>(fullLaunches[k]) == 0)
-                    CK(launch_gotoh_rows(std::get<2>(fullLaunches[k]), dTable + std::get<1>(fullLaunches[k]), dDesc, dState, arena,
+                    CK(launch_gotoh_rows(ctx.rowsMode, std::get<2>(fullLaunches[k]), dTable + std::get<1>(fullLaunches[k]), dDesc, dState, arena,
                                          dp.go, dp.ge, wk.aux[k]));
                 else
                     CK(launch_gotoh_fill(std::get<0>(fullLaunches[k]), std::get<2>(fullLaunches[k]), dTable + std::get<1>(fullLaunches[k]),
@@ -1288,10 +1290,6 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
         return set_err(nullptr, LARA_E_UNSUPPORTED, "greedy matching lookahead > 8 is not supported on the GPU path");
     if (params->num_iterations < 1 || params->max_nondecreasing < 0)
         return set_err(nullptr, LARA_E_INVALID, "invalid iteration parameters");
-    if (params->gap_open == params->gap_extend)
-        return set_err(nullptr, LARA_E_UNSUPPORTED,
-                       "gap open == gap extend switches the reference to linear gap costs (SeqAn dp_setup.h:322-325); "
-                       "not supported");
     int count = 0;
     cudaError_t e = cudaGetDeviceCount(&count);
     if (e != cudaSuccess || count == 0)
@@ -1328,6 +1326,11 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_WORKERPAIRS")) ctx->workerMinPairs = (size_t)std::max(1, std::atoi(e));
     ctx->P = *params;
     ctx->dp = make_dev_params(*params);
+    // gap costs outside go < ge: no band kernels.  open == extend: the scalar reference gets linear gap costs from SeqAn
+    // (global_alignment_unbanded.h:775-778), the SIMD build asks for affine ones (src/subgradient_solver_simd.hpp:257-263);
+    // open > extend: affine
+    if (params->gap_open == params->gap_extend) ctx->rowsMode = params->step_mode == LARA_STEP_SCALAR_FLOAT ? 1 : 0;
+    else if (params->gap_open > params->gap_extend) ctx->rowsMode = 2;
     try
     {
         for (int id : ids)
@@ -1537,10 +1540,6 @@ int lara_gpu_prepare_pairs(lara_ctx * ctx, int64_t n_pairs, int32_t const * idx_
         op.request = p;
         if (op.la > 32767)
             return set_err(ctx, LARA_E_UNSUPPORTED, "sequences longer than 32,767 nt are not supported (16-bit positions)");
-        if ((op.lb + 31) / 32 > kMaxR && !(ctx->dp.go < ctx->dp.ge))
-            return set_err(ctx, LARA_E_UNSUPPORTED, "shorter sequence of a pair exceeds " + std::to_string(32 * kMaxR) +
-                                                     " nt and gap open >= gap extend: neither the band kernels nor the row-by-row "
-                                                     "kernel cover these gap costs");
     }
     {
         // the post kernel keeps the lines of a pair in shared memory (kernels_post.cu: WarpSmem)

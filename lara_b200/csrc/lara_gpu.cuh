@@ -159,7 +159,8 @@ struct PairOutHdr
 cudaError_t launch_gotoh_fill(int R, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state,
                               int32_t * arena, int32_t const * negBuf, int32_t go, int32_t ge, cudaStream_t stream);
 // full-matrix DP fill, row by row, one block per pair of any size (kernels_rows.cu): pairs listed in pairIdx[0..n)
-cudaError_t launch_gotoh_rows(int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
+// mode 0: affine gap costs with go <= ge, 1: linear gap costs (Needleman-Wunsch), 2: affine with go > ge
+cudaError_t launch_gotoh_rows(int mode, int n, int32_t const * pairIdx, PairDesc const * desc, PairState * state, int32_t * arena,
                               int32_t go, int32_t ge, cudaStream_t stream);
 // band DP fill (kernels_band.cu) over warp groups of 32 / G pairs with the same band shape (G lanes per pair, blocks
 // of Q diagonals): pairIdx[0..nSlots) lists the groups slot by slot, -1 = empty slot

@@ -217,6 +217,59 @@ void gotoh_traceback(int la, int lb, std::vector<uint8_t> const & trace, std::ve
     std::reverse(ops.begin(), ops.end());
 }
 
+// ---------------------------------------------------------------------------------------------
+// Linear gap costs.  SeqAn's globalAlignment switches to Needleman-Wunsch when gap open == gap extend
+// (SeqAn:align/global_alignment_unbanded.h:775-778): one score matrix, recursion
+// SeqAn:align/dp_formula_linear.h:62-99 (vertical wins the tie against horizontal, the diagonal wins the tie against the
+// better gap), no end-cell correction (dp_algorithm_impl.h: _correctTraceValue does nothing for LinearGaps), traceback one
+// cell at a time (dp_traceback_impl.h:190-262 with TGapCosts = LinearGaps, :400-418).
+// ---------------------------------------------------------------------------------------------
+ScoreType nw_fill(int la, int lb, ScoreType const * pssm, ScoreType g, std::vector<uint8_t> & trace)
+{
+    size_t const stride = (size_t)lb + 1;
+    trace.assign((size_t)(la + 1) * stride, 0);
+    std::vector<ScoreType> S(lb + 1);
+    S[0] = 0;
+    trace[0] = T_NONE;
+    for (int r = 1; r <= lb; ++r) { S[r] = S[r - 1] + g; trace[r] = T_V | T_MAXV; }
+    for (int c = 1; c <= la; ++c)
+    {
+        uint8_t * tcol = &trace[(size_t)c * stride];
+        ScoreType diag = S[0];
+        S[0] = S[0] + g;
+        tcol[0] = T_H | T_MAXH;
+        ScoreType const * prow = pssm + (size_t)(c - 1) * lb;
+        for (int r = 1; r <= lb; ++r)
+        {
+            ScoreType const d = diag + prow[r - 1];
+            diag = S[r];
+            ScoreType const v = S[r - 1] + g, h = S[r] + g;
+            ScoreType gm; uint8_t t;
+            if (v < h) { gm = h; t = T_H | T_MAXH; } else { gm = v; t = T_V | T_MAXV; }
+            if (d < gm) { S[r] = gm; tcol[r] = t; } else { S[r] = d; tcol[r] = T_DIAG; }
+        }
+    }
+    return S[lb];
+}
+
+void nw_traceback(int la, int lb, std::vector<uint8_t> const & trace, std::vector<uint8_t> & ops)
+{
+    size_t const stride = (size_t)lb + 1;
+    ops.clear();
+    int c = la, r = lb;
+    while (c > 0 && r > 0)
+    {
+        uint8_t const tv = trace[(size_t)c * stride + r];
+        if (tv & T_DIAG) { --c; --r; ops.push_back(0); }
+        else if ((tv & T_MAXV) && (tv & T_V)) { --r; ops.push_back(1); }
+        else if ((tv & T_MAXH) && (tv & T_H)) { --c; ops.push_back(2); }
+        else break;
+    }
+    for (; r > 0; --r) ops.push_back(1);
+    for (; c > 0; --c) ops.push_back(2);
+    std::reverse(ops.begin(), ops.end());
+}
+
 // Lagrange::evaluateLines, src/lagrange.hpp:147-221
 ScoreType evaluate_lines(std::vector<uint8_t> const & ops, ScoreType go, ScoreType ge,
                          std::vector<int32_t> & la_, std::vector<int32_t> & lb_)
@@ -572,8 +625,18 @@ void solve_pair(lara_params const * P, SeqView const & sa, SeqView const & sb, i
     std::vector<uint8_t> trace, ops;
     for (;;)
     {
-        currentUpper = gotoh_fill(lag.la, lag.lb, lag.pssm.data(), P->gap_open, P->gap_extend, trace);
-        gotoh_traceback(lag.la, lag.lb, trace, ops);
+        // the scalar solver lets SeqAn choose (linear gap costs when open == extend); the SIMD solver asks for AffineGaps
+        // explicitly (src/subgradient_solver_simd.hpp:257-263)
+        if (P->gap_open == P->gap_extend && P->step_mode == LARA_STEP_SCALAR_FLOAT)
+        {
+            currentUpper = nw_fill(lag.la, lag.lb, lag.pssm.data(), P->gap_extend, trace);
+            nw_traceback(lag.la, lag.lb, trace, ops);
+        }
+        else
+        {
+            currentUpper = gotoh_fill(lag.la, lag.lb, lag.pssm.data(), P->gap_open, P->gap_extend, trace);
+            gotoh_traceback(lag.la, lag.lb, trace, ops);
+        }
         currentLower = lag.valid_solution(ops);
         if (currentUpper < bestUpper) { bestUpper = currentUpper; nondecreasing = 0; }
         if (currentLower > bestLower) { bestLower = currentLower; nondecreasing = 0; }

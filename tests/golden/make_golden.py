@@ -56,6 +56,13 @@ INPUTS = {
     "ct4x80": dict(gen=dict(seed=107, n=4, length=70, fmt="ct", lenmax=90, related=False),
                    cases=[("default", "scalar", []),
                           ("simd_pairs", "simd", ["-o", "pairs"])]),
+    # gap costs outside the common case: open == extend (SeqAn switches to Needleman-Wunsch, linear gap costs) and
+    # open cheaper than extend
+    "ebp6gaps": dict(gen=dict(seed=109, n=6, length=50, fmt="ebpseq", lenmax=75),
+                     cases=[("linear", "scalar", ["-n", "80", "-x", "-3", "-y", "-3"]),
+                            ("linear_simd", "simd", ["-n", "80", "-x", "-3", "-y", "-3"]),
+                            ("open_cheaper", "scalar", ["-n", "80", "-x", "-4", "-y", "-2"]),
+                            ("open_cheaper_simd_pairs", "simd", ["-n", "80", "-x", "-4", "-y", "-2", "-o", "pairs"])]),
     # -s: score matrix file read by SeqAn's loadScoreMatrix (src/parameters.hpp:306-323)
     "ebp6matrix": dict(gen=dict(seed=108, n=6, length=55, fmt="ebpseq", lenmax=70),
                        cases=[("s_matrix", "scalar", ["-n", "80", "-s", "@golden/matrix_test.txt"]),

@@ -51,7 +51,7 @@ def test_unsupported_options_are_refused(built):
     import lara_b200 as lb
     from lara_b200 import _lib
     lib = _lib.load()
-    for kw in (dict(matching=0), dict(gap_open=-16384, gap_extend=-16384), dict(num_iterations=0)):
+    for kw in (dict(matching=0), dict(matching=9), dict(num_iterations=0)):
         p = lb.Parameters()
         p.set(**kw)
         h = C.c_void_p()

@@ -106,6 +106,24 @@ def test_solve_long_unequal_pair(built):
     assert util.results_equal(got, want) is None, util.results_equal(got, want)
 
 
+@pytest.mark.parametrize("kw,env", [
+    (dict(gap_open=-3 * 8192, gap_extend=-3 * 8192), {}),                                # scalar build: SeqAn's linear gap costs
+    (dict(gap_open=-3 * 8192, gap_extend=-3 * 8192, step_mode=1), {}),                   # SIMD build: affine, everything ties
+    (dict(gap_open=-3 * 8192, gap_extend=-3 * 8192, step_mode=1), dict(LARA_B200_ROWS="1")),
+    (dict(gap_open=-2 * 8192, gap_extend=-4 * 8192), {}),                                # opening cheaper than extending
+    (dict(gap_open=-2 * 8192, gap_extend=-4 * 8192), dict(LARA_B200_ROWS="1")),
+    (dict(gap_open=-2 * 8192, gap_extend=-4 * 8192, step_mode=1), dict(LARA_B200_ROWS="1")),
+])
+def test_solve_unusual_gap_costs(built, kw, env, monkeypatch):
+    """Gap open >= gap extend: no band kernels (their closed forms need opening to be dearer than extending); linear
+    gap costs when the scalar reference would switch to Needleman-Wunsch, the three forms of the row-by-row kernel."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    files = util.make_input(seed=46, n=9, length=40, lenmax=120)
+    got, want, _ = _solve_both(files, num_iterations=70, max_nondecreasing=8, **kw)
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+
+
 def test_solve_negative_step(built):
     """SIMD-build arithmetic on skewed lengths for many iterations: the wrapping int32 product makes negative steps, so
     multipliers of +1 entries go up and those of -1 entries go down (every touched row is rescanned or raised by what
