@@ -853,18 +853,43 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         uint8_t const * __restrict__ seqA = in.seqCat + in.seqOff[d.seqFirst];
         uint8_t const * __restrict__ seqB = in.seqCat + in.seqOff[d.seqSecond];
         float const scale = st.scale;
+        // the row record of a line is loaded one round ahead of its use (the records were pulled into L2 when the kernel
+        // started, an L2 hit still takes longer than a round)
+        bool const hasRec = d.offRowRec != 0;
+        int4 const * __restrict__ rowRec = reinterpret_cast<int4 const *>(arena + d.offRowRec);
+        uint32_t abNext = lane < nLines ? sm.linesRev[nLines - 1 - lane] : 0u;
+        int4 recNext = make_int4(0, 0, 0, 0);
+        if (hasRec && lane < nLines) recNext = __ldg(rowRec + (abNext >> 16));
         for (int i0 = 0; i0 < nLines; i0 += 32)
         {
             int const i = i0 + lane;
             bool work = false;
             int e = -1;
+            uint32_t const ab = abNext;
+            int4 const rec = recNext;
+            if (i + 32 < nLines)
+            {
+                abNext = sm.linesRev[nLines - 1 - (i + 32)];
+                if (hasRec) recNext = __ldg(rowRec + (abNext >> 16));
+            }
             if (i < nLines)
             {
-                uint32_t const ab = sm.linesRev[nLines - 1 - i];
                 int const a = (int)(ab >> 16), b = (int)(ab & 0xffffu);
                 sm.lineOfA[a] = (int16_t)i;
-                int codeA;
-                e = edge_of(d, arena, a, b, work, codeA);
+                int codeA = -1;
+                if (hasRec)
+                {
+                    // narrow band: the row's active cells fit one word (edge_of)
+                    int const k = b - (a - d.dHi);
+                    codeA = rec.w;
+                    if (k >= 0 && k <= 31 && (((uint32_t)rec.y >> k) & 1u))
+                    {
+                        work = ((uint32_t)rec.z >> k) & 1u;
+                        e = rec.x + __popc((uint32_t)rec.y & ((1u << k) - 1u));
+                    }
+                }
+                else
+                    e = edge_of(d, arena, a, b, work, codeA);
                 if (e < 0) { sm.misc[11] = 1; work = false; }   // "Alignment match where no alignment edge is defined!"
                 else if (!work)
                 {
@@ -920,13 +945,17 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
         }
         if (!cycle) mark(x, rx);
     };
+    // the edge record of a line is loaded one group of 32 lines ahead of its use
+    int4 erNext = make_int4(0, 0, 0, 0);
+    if (lane < nWork) erNext = edge[sm.curE[lane]];
     for (int base = 0; base < nWork; base += 32)
     {
         int const e = base + lane < nWork ? sm.curE[base + lane] : -1;
         int const myLine = e >= 0 ? sm.workLine[base + lane] : 0;
         uint32_t const myCell = e >= 0 ? sm.linesRev[nLines - 1 - myLine] : 0u;
-        int4 er = make_int4(0, 0, 0, 0);
-        if (e >= 0) er = edge[e];
+        int4 er = erNext;
+        erNext = make_int4(0, 0, 0, 0);
+        if (base + 32 + lane < nWork) erNext = edge[sm.curE[base + 32 + lane]];
         lbSeq += er.x;
         int off = er.w;
         #pragma unroll
