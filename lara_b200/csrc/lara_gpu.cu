@@ -143,6 +143,10 @@ struct lara_ctx
     bool forceRows = false;                 // every pair without a band runs the row-by-row kernel (env LARA_B200_ROWS=1; tests)
     int refillMode = 1;                     // slot refill: 0 = set by set, 1 = as slots free up while the queue is long,
                                             // 2 = always as slots free up (env LARA_B200_REFILL)
+    double memBudget = 0;                   // test hook: bytes the workers of a device may hold together, 0 = automatic
+                                            // (env LARA_B200_MEMBUDGET, in MB)
+    double refillFirstShare = 0.8;          // share of a worker's memory budget the first cohort takes when slots will be
+                                            // refilled as they free up (env LARA_B200_REFILLSHARE)
     size_t workerMinPairs = 2048;           // a device runs one worker per this many pairs, up to nWorkers (env LARA_B200_WORKERPAIRS)
 };
 
@@ -337,6 +341,7 @@ struct Cohort
     int base = 0, n = 0, live = 0;
     int maxLa = 0, maxLb = 0, maxK = 0;
     std::vector<void *> pooled;                 // per-pair arrays from the stream-ordered pool
+    int64_t pooledBytes = 0;
 };
 
 struct ResidentSet
@@ -362,6 +367,7 @@ struct ResidentSet
     int64_t liveLanes16 = 0;                    // lanes of the live pairs' fill with blocks of 16 diagonals
     bool have24 = false;
     bool slabFree = true;                       // no live pair has arrays in the worker's slab: the next cohort may take it
+    int64_t bytesHeld = 0, keepBytes = 0;       // bytes of the stream-ordered pool the set holds now (all / the groups' arrays)
     // slot table on the device and its launch geometry
     int32_t * dTable = nullptr;
     size_t tableCap = 0;
@@ -436,8 +442,12 @@ struct ResidentSet
                 rg.ptr = wk.slab + atInts;
             else
             {
-                CK(cudaMallocAsync((void **)&rg.ptr, (size_t)std::max<int64_t>(sizeInts, 1) * 4, st));
+                int64_t const b = std::max<int64_t>(sizeInts, 1) * 4;
+                CK(cudaMallocAsync((void **)&rg.ptr, (size_t)b, st));
                 owner.push_back(rg.ptr);
+                bytesHeld += b;
+                if (&owner == &keep) keepBytes += b;
+                else if (&owner == &cohorts.back().pooled) cohorts.back().pooledBytes += b;
             }
             rg.size = sizeInts;
             rg.baseDelta = rg.ptr - arena;
@@ -504,10 +514,12 @@ struct ResidentSet
         // edge filter scratch (forward prefix scores): lives only until the filter has run
         Region rS;
         std::vector<void *> scratchOwner;
+        int64_t scratchBytes = 0;
         {
             int64_t sizeS = 0;
             for (int i = 0; i < n; ++i) sizeS += align4((int64_t)cd[i].la * cd[i].lb + 6ll * (cd[i].la + 1));
             region_alloc(rS, sizeS, al256(sizeA), scratchOwner);
+            if (!scratchOwner.empty()) scratchBytes = std::max<int64_t>(sizeS, 1) * 4;
             for (int i = 0; i < n; ++i)
                 cd[i].offScratch = rS.take((int64_t)cd[i].la * cd[i].lb + 6ll * (cd[i].la + 1));
         }
@@ -522,6 +534,7 @@ struct ResidentSet
         CK(cudaMemcpyAsync(cd, dCd, sizeof(PairDesc) * (size_t)n, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         for (void * f : scratchOwner) CK(cudaFreeAsync(f, st));
+        bytesHeld -= scratchBytes;
         lap("edge filter (sync)");
         wk.stats.kernel_launches += 1;
         // ---- band geometry of every pair; slots in existing groups, new groups for the rest ---------------------
@@ -771,9 +784,11 @@ struct ResidentSet
         {
             for (void * f : c.pooled) CK(cudaFreeAsync(f, s));
             c.pooled.clear();
+            bytesHeld -= c.pooledBytes; c.pooledBytes = 0;
         }
         for (void * f : keep) CK(cudaFreeAsync(f, s));
         keep.clear();
+        bytesHeld -= keepBytes; keepBytes = 0;
         groups.clear();
         for (int32_t & g : groupOf) g = -1;
         fullPairs.clear();
@@ -887,6 +902,7 @@ struct ResidentSet
         {
             for (void * f : c.pooled) CK(cudaFreeAsync(f, s));
             c.pooled.clear();
+            bytesHeld -= c.pooledBytes; c.pooledBytes = 0;
         }
     }
 
@@ -956,15 +972,34 @@ struct ResidentSet
 
 // Pairs per batch from the free device memory and a per-pair estimate (exact for the length dependent
 // part, heuristic for the edge/interaction arrays whose sizes are only known after set-up).
-size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers, double & bytes)
+// Bytes of device memory a pair holds while it is resident, estimated from its lengths and the densities measured on a
+// sample of the device's pairs (run_device) with a safety factor: bitmap C / 8 + per edge 36 + per interaction 56 + DP
+// arrays + lines, candidates, row starts.  The edge filter's scratch (4 C) is held during the set-up of a cohort only.
+// `scale`: correction of the resident part from the cohorts a worker has admitted so far (run_worker).
+double pair_bytes(Device const & dv, OrientedPair const & op, double scale = 1.0)
 {
+    double const cells = std::max(dv.pilot.cells, 1.0);
+    double const ePerCell = 1.3 * dv.pilot.edges / cells, dPerCell = 1.3 * dv.pilot.inters / cells, dpPerCell = 1.3 * dv.pilot.dpBytes / cells;
+    double const C = (double)op.la * op.lb;
+    return 4.0 * C + scale * (C / 8 + (36.0 * ePerCell + 56.0 * dPerCell + dpPerCell) * C + 64.0 * (op.la + op.lb) + 4096);
+}
+
+// What one of the device's nWorkers workers may hold: its share of 70 % of the device, but not more than what is free
+// now plus the slabs the workers already hold (other contexts or processes may live on the same device).
+double worker_budget(lara_ctx const & ctx, Device & dv, int nWorkers)
+{
+    if (ctx.memBudget > 0) return ctx.memBudget / (double)nWorkers;
     size_t freeB = 0, totalB = 0;
     cudaMemGetInfo(&freeB, &totalB);
-    // what this device's workers may use together: 55 % of the device, but not more than what is free now plus the
-    // slabs they already hold (other contexts or processes may live on the same device)
     double held = 0;
     for (Worker const & w : dv.workers) held += 4.0 * (double)w.slabInts;
-    double const budget = std::min(0.55 * (double)totalB, 0.9 * ((double)freeB + held)) / (double)nWorkers;
+    return std::min(0.70 * (double)totalB, 0.9 * ((double)freeB + held)) / (double)nWorkers;
+}
+
+size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers, double & bytes, double budgetScale = 1.0,
+                   size_t * slotLimit = nullptr)
+{
+    double const budget = budgetScale * worker_budget(ctx, dv, nWorkers);
     double used = 0;
     size_t k = begin;
     size_t hardCap = ctx.batchPairsCap ? ctx.batchPairsCap : ctx.batchPairsDefault;
@@ -976,22 +1011,15 @@ size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers, doub
         nB = (nB + (size_t)nWorkers - 1) / (size_t)nWorkers * (size_t)nWorkers;
         hardCap = std::max<size_t>((N + nB - 1) / nB, std::min<size_t>(N, 1024));
     }
-    // densities measured on a sample of this device's pairs (run_device), with a safety factor
-    double const ePerCell = 1.3 * dv.pilot.edges / std::max(dv.pilot.cells, 1.0);
-    double const dPerCell = 1.3 * dv.pilot.inters / std::max(dv.pilot.cells, 1.0);
-    double const dpPerCell = 1.3 * dv.pilot.dpBytes / std::max(dv.pilot.cells, 1.0);
     while (k < dv.pairs.size() && k - begin < hardCap)
     {
-        OrientedPair const & op = dv.pairs[k];
-        double const C = (double)op.la * op.lb;
-        // bytes: filter scratch 4 C (set-up only) + bitmap C / 8 + per edge 36 + per interaction 56 + DP arrays
-        // + lines, candidates, row starts
-        double const per = 4.0 * C + C / 8 + (36.0 * ePerCell + 56.0 * dPerCell + dpPerCell) * C + 64.0 * (op.la + op.lb) + 4096;
+        double const per = pair_bytes(dv, dv.pairs[k]);
         if (used + per > budget && k > begin) break;
         used += per;
         ++k;
     }
     bytes = used;
+    if (slotLimit) *slotLimit = hardCap;
     return k;
 }
 
@@ -1006,17 +1034,49 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
         cudaStream_t const s = wk.stream;
         size_t begin, end;
         double bytes = 0;
+        double const budget = worker_budget(ctx, dv, nWorkers);
+        size_t slotLimit = 0, roundPairs = 0;       // most pairs live at once; pairs of a set that takes the whole budget
+        double estScale = 1.0;                      // resident bytes per pair: measured / estimated, over the cohorts so far
         {
             std::lock_guard<std::mutex> lock(dv.queueMutex);
             begin = dv.nextBegin;
-            end = begin < dv.pairs.size() ? batch_limit(ctx, dv, begin, nWorkers, bytes) : begin;
+            end = begin < dv.pairs.size() ? batch_limit(ctx, dv, begin, nWorkers, bytes, 1.0, &slotLimit) : begin;
+            roundPairs = end - begin;
+            if (end > begin && ctx.refillMode != 0 &&
+                (ctx.refillMode == 2 || dv.pairs.size() - begin > 3 * (end - begin) * (size_t)nWorkers))
+            {
+                // The queue is long: slots will be refilled as they free up.  A cohort gives its arrays back when its
+                // last pair has finished, so the set holds somewhat more than its live pairs' arrays: the first cohort
+                // leaves room for that, and its arrays come from the pool (arrays in the worker's slab could only be
+                // given back when the whole set has drained).
+                end = batch_limit(ctx, dv, begin, nWorkers, bytes, ctx.refillFirstShare);
+                bytes = 0;
+            }
             dv.nextBegin = end;
         }
         if (end > begin)
         {
-            size_t const capacity = end - begin;
+            size_t const capacity = std::max(end - begin, slotLimit);
             rs.init(dv.pairs.size());
+            // estimate of the resident bytes of the pairs [b, e) with scale 1 (under the queue's order: no lock needed)
+            auto resident_estimate = [&](size_t b, size_t e)
+            {
+                double x = 0;
+                for (size_t k = b; k < e; ++k) x += pair_bytes(dv, dv.pairs[k]) - 4.0 * (double)dv.pairs[k].la * dv.pairs[k].lb;
+                return x;
+            };
+            // after a cohort from the pool: how its bytes compare with the estimate (10 % on top; never above the a-priori one)
+            auto calibrate = [&](size_t b, size_t e, int64_t heldBefore)
+            {
+                if (e - b < 256) return;
+                double const ratio = (double)(rs.bytesHeld - heldBefore) / std::max(resident_estimate(b, e), 1.0);
+                estScale = std::min(1.0, std::max(0.3, 1.1 * ratio));
+                if (ctx.verbose)
+                    std::fprintf(stderr, "[lara_b200] dev %d cohort %zu+%zu: %.2f GB resident, %.2f of the estimate; set holds %.2f of %.2f GB\n",
+                                 dv.id, b, e - b, (double)(rs.bytesHeld - heldBefore) / 1e9, ratio, (double)rs.bytesHeld / 1e9, budget / 1e9);
+            };
             rs.admit(begin, end, s, bytes);
+            if (bytes == 0) calibrate(begin, end, 0);
             rs.rebuild_table();
             int const nIter = ctx.P.num_iterations;
             // finished list window read by the host after every block of steps: [0] count, [1 ..] the entries from
@@ -1033,7 +1093,7 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
             size_t winStart[2] = {0, 0};
             int steps = 0, block = 0, nextBlockLen = 1;
             // every set may run numIterations steps, and its end is noticed up to two blocks of steps late
-            int64_t const maxSteps = ((int64_t)nIter + 64) * (int64_t)(dv.pairs.size() / capacity + 3) + 64;
+            int64_t const maxSteps = ((int64_t)nIter + 64) * (int64_t)(20 * dv.pairs.size() / std::max<size_t>(end - begin, 1) + 3) + 64;
             bool more = true;                               // the queue may still hold pairs
             bool pendingSplice = false;
             int outstanding = -1;                           // buffer of the block whose results have not been read yet
@@ -1092,17 +1152,34 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
                         std::lock_guard<std::mutex> lock(dv.queueMutex);
                         queued = dv.pairs.size() - std::min(dv.pairs.size(), dv.nextBegin);
                     }
-                    bool const eager = ctx.refillMode == 2 || (ctx.refillMode == 1 && queued > 2 * capacity * (size_t)nWorkers);
-                    if ((eager && freeSlots >= std::max<size_t>(capacity / 10, 1)) || rs.live == 0)
+                    roundPairs = std::max(roundPairs, (size_t)rs.live);
+                    bool const eager = ctx.refillMode == 2 || (ctx.refillMode == 1 && queued > 2 * roundPairs * (size_t)nWorkers);
+                    size_t const minCohort = std::max<size_t>((size_t)rs.live / 10, 1);
+                    if ((eager && freeSlots >= minCohort) || rs.live == 0)
                     {
                         size_t b2, e2;
+                        bool wait = false;
                         {
+                            // as many of the free slots as the worker's memory budget has room for, counted from what
+                            // the set holds now (a drained set gives everything back first)
                             std::lock_guard<std::mutex> lock(dv.queueMutex);
                             b2 = dv.nextBegin;
-                            e2 = std::min(dv.pairs.size(), b2 + std::max<size_t>(freeSlots, 1));
+                            size_t const last = std::min(dv.pairs.size(), b2 + std::max<size_t>(freeSlots, 1));
+                            double const held = rs.live == 0 ? 0.0 : (double)rs.bytesHeld;
+                            double est = 0;
+                            for (e2 = b2; e2 < last; ++e2)
+                            {
+                                double const per = pair_bytes(dv, dv.pairs[e2], estScale);
+                                if (held + est + per > budget && (e2 > b2 || rs.live > 0)) break;
+                                est += per;
+                            }
+                            // too little room for a cohort worth its set-up: wait for running cohorts to give memory back
+                            wait = rs.live > 0 && e2 < last && e2 - b2 < minCohort;
+                            if (wait) e2 = b2;
                             dv.nextBegin = e2;
                         }
-                        if (e2 > b2)
+                        if (wait) {}
+                        else if (e2 > b2)
                         {
                             // the slots are known to be free: their pairs were reported by a block that has completed
                             double bytes2 = 0;
@@ -1112,7 +1189,9 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
                                 rs.begin_new_set(rs.side);
                                 bytes2 = (double)wk.slabInts * 4;       // what does not fit the slab comes from the pool
                             }
+                            int64_t const heldBefore = rs.bytesHeld;
                             rs.admit(b2, e2, rs.side, bytes2);
+                            if (bytes2 == 0) calibrate(b2, e2, heldBefore);
                             CK(cudaEventRecord(rs.evSide, rs.side));
                             pendingSplice = true;
                         }
@@ -1323,6 +1402,8 @@ int lara_gpu_create(lara_ctx ** out, lara_params const * params, int n_devices, 
     if (char const * e = std::getenv("LARA_B200_SPLITWARPS")) ctx->bandSplitWarps = std::max(1, std::atoi(e));
     if (char const * e = std::getenv("LARA_B200_ROWS")) ctx->forceRows = std::atoi(e) != 0;
     if (char const * e = std::getenv("LARA_B200_REFILL")) ctx->refillMode = std::max(0, std::min(2, std::atoi(e)));
+    if (char const * e = std::getenv("LARA_B200_MEMBUDGET")) ctx->memBudget = 1e6 * std::max(0.0, std::atof(e));
+    if (char const * e = std::getenv("LARA_B200_REFILLSHARE")) ctx->refillFirstShare = std::max(0.1, std::min(1.0, std::atof(e)));
     if (char const * e = std::getenv("LARA_B200_WORKERPAIRS")) ctx->workerMinPairs = (size_t)std::max(1, std::atoi(e));
     ctx->P = *params;
     ctx->dp = make_dev_params(*params);
