@@ -210,6 +210,26 @@ int lara_gpu_gotoh_band_batch(lara_ctx * ctx, int32_t n_problems, int32_t lenA, 
 int lara_gpu_edge_filter(lara_ctx * ctx, uint8_t const * seqA, int32_t lenA, uint8_t const * seqB, int32_t lenB,
                          uint8_t * active, int32_t * opt_score);
 
+/*
+ * lara_gpu_edge_filter for callers that cannot let the library allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same computation and same results as lara_gpu_edge_filter, but
+ *   - every pointer is a DEVICE pointer of the context's first device, allocated by the caller:
+ *     d_seqA[lenA], d_seqB[lenB] (Rna5 codes), d_active[lenA*lenB] (one byte per cell), d_opt_score[1] (may be NULL);
+ *   - the pair record, the bitmap and the filter's scratch (lenA*lenB + 6*(lenA+1) ints) live in ONE file-scope
+ *     `static __device__` array of LARA_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until the
+ *     process exits; the call performs no cudaMalloc / cudaFree / stream-ordered allocation (the first call on a device
+ *     looks the array's device address up with cudaGetSymbolAddress, later calls only launch kernels);
+ *   - sizes whose scratch does not fit (about lenA*lenB > 1.0 M cells, e.g. beyond 1,000 x 1,000 nt) are refused with
+ *     LARA_E_UNSUPPORTED and a message that states the need;
+ *   - all calls share the array: a call overwrites what the previous one left (nothing needs to be cleared by the
+ *     caller), and two calls that overlap on one GPU (two threads, two contexts) RACE - serialise them.
+ * Returns after the context's stream has been synchronised.
+ */
+#define LARA_NOALLOC_SCRATCH_BYTES (4 * 1024 * 1024)
+int lara_gpu_edge_filter_noalloc(lara_ctx * ctx, uint8_t const * d_seqA, int32_t lenA, uint8_t const * d_seqB, int32_t lenB,
+                                 uint8_t * d_active, int32_t * d_opt_score);
+
 /* Integer-issue microbenchmark for the roofline denominator: returns Gop/s (lane-ops) of
  * dependent-free IADD/VIMNMX streams on the current device. kind: 0 = IADD3, 1 = VIMNMX, 2 = mixed DP mix */
 int lara_gpu_int_issue_rate(lara_ctx * ctx, int kind, double * gops);

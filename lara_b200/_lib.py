@@ -117,6 +117,7 @@ GPU_SYMBOLS = {
     "lara_gpu_gotoh_band_batch": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
                                             C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "lara_gpu_edge_filter": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, _P(C.c_int32)]),
+    "lara_gpu_edge_filter_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "lara_gpu_int_issue_rate": (C.c_int, [C.c_void_p, C.c_int, _P(C.c_double)]),
 }
 HOST_SYMBOLS = {

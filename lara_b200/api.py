@@ -303,6 +303,11 @@ class Context:
                                                    active.ctypes.data, C.byref(opt)))
         return active.reshape(len(a), len(b)), opt.value
 
+    def edge_filter_noalloc(self, d_seq_a, len_a, d_seq_b, len_b, d_active, d_opt_score=0):
+        """lara_gpu_edge_filter_noalloc: DEVICE addresses (ints) of caller-allocated buffers; the library allocates nothing."""
+        self._check(self._lib.lara_gpu_edge_filter_noalloc(self._h, d_seq_a, len_a, d_seq_b, len_b, d_active,
+                                                           d_opt_score or None))
+
     def int_issue_rate(self, kind=0):
         g = C.c_double()
         self._check(self._lib.lara_gpu_int_issue_rate(self._h, kind, C.byref(g)))

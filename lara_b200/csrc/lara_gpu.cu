@@ -2108,3 +2108,129 @@ int lara_gpu_int_issue_rate(lara_ctx * ctx, int kind, double * gops)
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// Entry point that allocates nothing (no counterpart in the reference; see include/lara_b200.h)
+// ---------------------------------------------------------------------------------------------------
+namespace
+{
+
+// Everything lara_gpu_edge_filter() takes from cudaMalloc, in one array that every device which loads the library
+// holds until the process exits: pair record, solver state, sequence offsets, the two sequences, the active-edge
+// bitmap and the edge filter's scratch (forward prefix scores + row buffers).  Shared by all calls: a call overwrites
+// what the call before it left, and two calls that overlap on a device race.
+constexpr int64_t kNoAllocInts = (int64_t)LARA_NOALLOC_SCRATCH_BYTES / 4;
+static __device__ __align__(256) int32_t g_noAllocScratch[kNoAllocInts];
+
+// header of the array, in ints (every part starts on a 256-byte boundary)
+constexpr int64_t kNaDesc = 0;                          // PairDesc
+constexpr int64_t kNaState = 128;                       // PairState
+constexpr int64_t kNaSeqOff = 192;                      // int64_t[3]
+constexpr int64_t kNaBody = 256;                        // sequences, bitmap, filter scratch
+static_assert(sizeof(PairDesc) <= (kNaState - kNaDesc) * 4, "pair record outgrew its part of the scratch header");
+static_assert(sizeof(PairState) <= (kNaSeqOff - kNaState) * 4, "solver state outgrew its part of the scratch header");
+
+inline int64_t align64(int64_t x) { return (x + 63) & ~(int64_t)63; }
+
+// device address of g_noAllocScratch per device: in host code the array's name is a host-side stand-in, only
+// cudaGetSymbolAddress (with the device current) gives what a kernel can use
+std::mutex g_noAllocMutex;
+std::map<int, int32_t *> g_noAllocPtr;
+
+int32_t * noalloc_scratch(int device)
+{
+    std::lock_guard<std::mutex> lock(g_noAllocMutex);
+    auto it = g_noAllocPtr.find(device);
+    if (it != g_noAllocPtr.end()) return it->second;
+    CK(cudaSetDevice(device));
+    int32_t * p = nullptr;
+    CK(cudaGetSymbolAddress((void **)&p, g_noAllocScratch));
+    if (!p) throw std::runtime_error("cudaGetSymbolAddress returned a null address for the scratch array");
+    g_noAllocPtr[device] = p;
+    return p;
+}
+
+// writes the header of the scratch array (everything that must not carry over from the call before) and copies the
+// two sequences in
+__global__ void noalloc_init_kernel(int32_t * __restrict__ scratch, PairDesc d, uint8_t const * __restrict__ seqA,
+                                    uint8_t const * __restrict__ seqB)
+{
+    uint8_t * cat = (uint8_t *)(scratch + kNaBody);
+    int const n = d.la + d.lb;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        cat[i] = i < d.la ? seqA[i] : seqB[i - d.la];
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        *(PairDesc *)(scratch + kNaDesc) = d;
+        PairState st{};
+        *(PairState *)(scratch + kNaState) = st;
+        int64_t * off = (int64_t *)(scratch + kNaSeqOff);
+        off[0] = 0; off[1] = d.la; off[2] = (int64_t)d.la + d.lb;
+    }
+}
+
+// bitmap -> one byte per cell, optimum score -> the caller's word
+__global__ void noalloc_expand_kernel(int32_t const * __restrict__ scratch, uint8_t * __restrict__ active,
+                                      int32_t * __restrict__ optScore)
+{
+    PairDesc const & d = *(PairDesc const *)(scratch + kNaDesc);
+    uint32_t const * bits = (uint32_t const *)(scratch + d.offBits);
+    int64_t const cells = (int64_t)d.la * d.lb;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < cells; i += (int64_t)gridDim.x * blockDim.x)
+    {
+        int const a = (int)(i / d.lb), b = (int)(i - (int64_t)a * d.lb);
+        active[i] = (uint8_t)((bits[(size_t)a * d.bitWords + (b >> 5)] >> (b & 31)) & 1u);
+    }
+    if (optScore && blockIdx.x == 0 && threadIdx.x == 0)
+        *optScore = ((PairState const *)(scratch + kNaState))->optScore;
+}
+
+} // namespace
+
+extern "C" {
+
+int lara_gpu_edge_filter_noalloc(lara_ctx * ctx, uint8_t const * d_seqA, int32_t lenA, uint8_t const * d_seqB, int32_t lenB,
+                                 uint8_t * d_active, int32_t * d_opt_score)
+{
+    if (!ctx || !d_seqA || !d_seqB || lenA < 1 || lenB < 1 || !d_active) return set_err(ctx, LARA_E_INVALID, "bad argument");
+    int64_t const bitWords = (lenB + 31) / 32;
+    int64_t const seqInts = align64(((int64_t)lenA + lenB + 3) / 4);
+    int64_t const bitInts = align64((int64_t)lenA * bitWords);
+    int64_t const filterInts = (int64_t)lenA * lenB + 6ll * ((int64_t)lenA + 1);
+    int64_t const need = kNaBody + seqInts + bitInts + filterInts;
+    if (need > kNoAllocInts)
+        return set_err(ctx, LARA_E_UNSUPPORTED,
+                       "lara_gpu_edge_filter_noalloc: " + std::to_string(lenA) + " x " + std::to_string(lenB) + " nt needs " +
+                       std::to_string(need * 4) + " bytes of scratch, the static array holds " +
+                       std::to_string((long long)LARA_NOALLOC_SCRATCH_BYTES) + " (use lara_gpu_edge_filter)");
+    Device & dv = ctx->devs[0];
+    cudaStream_t const s = dv.stream;
+    try
+    {
+        CK(cudaSetDevice(dv.id));
+        int32_t * const scratch = noalloc_scratch(dv.id);
+        PairDesc d{};
+        d.la = lenA; d.lb = lenB; d.seqFirst = 0; d.seqSecond = 1; d.bitWords = (int32_t)bitWords;
+        d.offBits = kNaBody + seqInts;
+        d.offScratch = kNaBody + seqInts + bitInts;
+        DevInputs in{};
+        in.seqCat = (uint8_t const *)(scratch + kNaBody);
+        in.seqOff = (int64_t const *)(scratch + kNaSeqOff);
+        int const cpBlocks = (int)std::min<int64_t>(((int64_t)lenA + lenB + 255) / 256, 64);
+        noalloc_init_kernel<<<cpBlocks, 256, 0, s>>>(scratch, d, d_seqA, d_seqB);
+        CK(cudaGetLastError());
+        CK(launch_edge_filter(1, (PairDesc *)(scratch + kNaDesc), (PairState *)(scratch + kNaState), scratch, in, ctx->dp,
+                              lenB, s));
+        int const exBlocks = (int)std::min<int64_t>(((int64_t)lenA * lenB + 255) / 256, 1184);
+        noalloc_expand_kernel<<<exBlocks, 256, 0, s>>>(scratch, d_active, d_opt_score);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(s));
+    }
+    catch (std::exception const & ex)
+    {
+        return set_err(ctx, LARA_E_CUDA, ex.what());
+    }
+    return LARA_OK;
+}
+
+} // extern "C"
