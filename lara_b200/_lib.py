@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblara_b200.so")
+# LARA_B200_LIB: another build of the same library (developer A/B runs: tools/sweep_env.sh); never a different implementation
+LIB_PATH = os.environ.get("LARA_B200_LIB") or os.path.join(_HERE, "liblara_b200.so")
 
 
 class LaraParams(C.Structure):

@@ -45,6 +45,10 @@
 
 #include <cstdlib>
 
+#ifndef LARA_BAND_DPX
+#define LARA_BAND_DPX 0
+#endif
+
 namespace lara
 {
 
@@ -95,12 +99,24 @@ __device__ __forceinline__ int32_t band_run(int32_t (&S)[Q], int32_t (&V)[Q], in
         int32_t const us = (j + 1 < Q) ? S[j + 1] : sU;
         int32_t const uv = (j + 1 < Q) ? V[j + 1] : vU;
         int32_t const dd = S[j] + sub[j];
+#if LARA_BAND_DPX
+        // three-operand forms (VIADDMNMX, IADD3): max(x + ge, y) in one instruction, and the decision as the sign of
+        // (x + ge) - max, which is negative exactly when the opening won (extension wins ties) -- 15 instructions per
+        // cell instead of 17, and the H chain along the run is one instruction per cell.  (The DPX max-with-predicate
+        // __vibmax_s32 is ISETP + SEL on sm_100a: no gain over subtraction + funnel shift.)
+        int32_t const vo = us + go;
+        int32_t const v = __viaddmax_s32(uv, ge, vo);
+        p2 = __funnelshift_l((uint32_t)(uv + ge - v), p2, 1);           // V opened   (extension wins ties)
+        int32_t const hn = __viaddmax_s32(h, ge, m);
+        p3 = __funnelshift_l((uint32_t)(h + ge - hn), p3, 1);           // H opened   (extension wins ties)
+#else
         int32_t const ve = uv + ge, vo = us + go;
         int32_t const v = max(ve, vo);
         p2 = __funnelshift_l((uint32_t)(ve - vo), p2, 1);               // V opened   (extension wins ties)
         int32_t const he = h + ge;
         int32_t const hn = max(he, m);
         p3 = __funnelshift_l((uint32_t)(he - m), p3, 1);                // H opened   (extension wins ties)
+#endif
         int32_t const mx = max(dd, v);
         int32_t const s = max(mx, hn);
         p1 = __funnelshift_l((uint32_t)(v - hn), p1, 1);                // gap from H (vertical wins ties)
@@ -566,7 +582,7 @@ gotoh_band_kernel(BandClassTable const tab, int32_t const * __restrict__ pairIdx
 {
     int c = 0;
     while (c + 1 < tab.n && (int)blockIdx.x >= tab.firstBlock[c + 1]) ++c;
-    int const warp = ((int)blockIdx.x - tab.firstBlock[c]) * 4 + (int)(threadIdx.x >> 5);
+    int const warp = ((int)blockIdx.x - tab.firstBlock[c]) * (int)(blockDim.x >> 5) + (int)(threadIdx.x >> 5);
     int32_t const * __restrict__ slots = pairIdx + tab.slotOffset[c];
     int const nSlots = tab.nSlots[c];
     switch (tab.shape[c])
@@ -597,11 +613,16 @@ cudaError_t launch_gotoh_band_multi(int nClasses, BandLaunch const * cls, int32_
     BandClassTable tab{};
     int blocks = 0;
     bool anyOne = false;
+    // warps per block (LARA_B200_FILLWARPS = 1, 2, 4; default 4).  Smaller blocks would find room on an SM sooner while the
+    // post kernel of another resident set holds its registers: measured no gain, alone or with the fill on a stream of the
+    // highest priority (profiles/README.md r2m)
+    static int const wpb = []() { char const * e = std::getenv("LARA_B200_FILLWARPS"); int v = e ? std::atoi(e) : 4;
+                                  return v == 1 || v == 2 ? v : 4; }();
     for (int k = 0; k < nClasses; ++k)
     {
         if (cls[k].nSlots <= 0) continue;
         if (tab.n >= kMaxBandClasses || !band_shape_supported(cls[k].G, cls[k].Q)) return cudaErrorInvalidValue;
-        int const slotsPerBlock = 4 * (32 / cls[k].G);
+        int const slotsPerBlock = wpb * (32 / cls[k].G);
         // LARA_B200_FUSED=1: the one-thread-per-pair shapes run the two-rows-at-a-time body (same results; measured no
         // faster on B200: profiles/README.md r2, so the generic body with its lower register count is the default)
         static bool const fused = []() { char const * e = std::getenv("LARA_B200_FUSED"); return e && std::atoi(e) != 0; }();
@@ -615,8 +636,8 @@ cudaError_t launch_gotoh_band_multi(int nClasses, BandLaunch const * cls, int32_
     }
     if (blocks == 0) return cudaSuccess;
     tab.firstBlock[tab.n] = blocks;
-    if (anyOne) gotoh_band_kernel<true><<<blocks, 128, 0, stream>>>(tab, pairIdx, desc, state, arena, go, ge);
-    else gotoh_band_kernel<false><<<blocks, 128, 0, stream>>>(tab, pairIdx, desc, state, arena, go, ge);
+    if (anyOne) gotoh_band_kernel<true><<<blocks, 32 * wpb, 0, stream>>>(tab, pairIdx, desc, state, arena, go, ge);
+    else gotoh_band_kernel<false><<<blocks, 32 * wpb, 0, stream>>>(tab, pairIdx, desc, state, arena, go, ge);
     return cudaGetLastError();
 }
 
