@@ -567,11 +567,17 @@ band_body_one(int const warp, int nSlots, int32_t const * __restrict__ pairIdx, 
 // shape with the most slots first), a block looks up its part in the class table and runs that shape's body.  Separate
 // launches per shape had to run side by side on streams (fork / join events every iteration), and a shape with a
 // handful of pairs then set the latency of the whole iteration step.
+#if defined(LARA_BAND_DEV) && LARA_BAND_DEV == 1          /* developer builds for SASS inspection: one shape only */
+#define LARA_BAND_SHAPES(X) X(2, 8)
+#elif defined(LARA_BAND_DEV) && LARA_BAND_DEV == 2
+#define LARA_BAND_SHAPES(X) X(1, 16)
+#else
 #define LARA_BAND_SHAPES(X) \
     X(1, 16) X(2, 16) X(4, 16) X(8, 16) X(16, 16) X(32, 16) \
     X(1, 12) \
     X(2, 8) X(4, 8) X(8, 8) X(16, 8) X(32, 8) \
     X(4, 4) X(8, 4) X(16, 4) X(32, 4)
+#endif
 
 // kOne: the launch has one-thread-per-pair classes in their two-rows-at-a-time form (more registers per thread; a
 // launch without such classes runs the instantiation without them and keeps its occupancy).

@@ -11,6 +11,7 @@
 #include "lara_gpu.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -76,6 +77,9 @@ struct Worker
 struct Pilot
 {
     double cells = 0, edges = 0, inters = 0, dpBytes = 0;
+    int bandSlack = 0;      // largest (diagonals the active edges span) - (la - lb + 1) of the sample: what a band needs beyond
+                            // the diagonals between the matrix's two corners
+    bool band = false;      // the sample ran the band kernels
 };
 
 // All device-side resources of one GPU.
@@ -234,6 +238,33 @@ DevParams make_dev_params(lara_params const & P)
     return d;
 }
 
+// cudaMallocAsync that survives a full pool: the workers of a device size their sets from an ESTIMATE of what a pair will
+// hold, and blocks freed on one stream are not at once usable from another.  On "out of memory" the device is drained
+// (pending cudaFreeAsync calls of all workers take effect), the pool's cached blocks go back to the driver, and the call
+// is repeated; while another worker still holds its set the wait goes on in steps of 10 ms, 20 times at most.
+cudaError_t malloc_async_retry(void ** p, size_t bytes, cudaStream_t st)
+{
+    // test hook LARA_B200_FAILALLOC=k: every k-th call is told "out of memory" once before it is made
+    char const * const fe = std::getenv("LARA_B200_FAILALLOC");
+    int const failEvery = fe ? std::atoi(fe) : 0;
+    static std::atomic<int> calls{0};
+    bool const pretend = failEvery > 0 && (++calls % failEvery) == 0;
+    cudaError_t e = pretend ? cudaErrorMemoryAllocation : cudaMallocAsync(p, bytes, st);
+    for (int attempt = 0; e == cudaErrorMemoryAllocation && attempt < 20; ++attempt)
+    {
+        (void)cudaGetLastError();
+        cudaError_t s2 = cudaDeviceSynchronize();
+        if (s2 != cudaSuccess) return s2;
+        int dev = 0;
+        cudaMemPool_t pool = nullptr;
+        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess)
+            (void)cudaMemPoolTrimTo(pool, 0);
+        e = cudaMallocAsync(p, bytes, st);
+        if (e == cudaErrorMemoryAllocation) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+    }
+    return e;
+}
+
 inline int64_t align4(int64_t x) { return (x + 3) & ~(int64_t)3; }
 
 // Bump allocator over one device allocation; offsets are relative to the batch's base pointer (in ints).
@@ -384,9 +415,9 @@ struct ResidentSet
     void init(size_t maxPairs)
     {
         pairCap = std::max<size_t>(maxPairs, 1);
-        CK(cudaMallocAsync((void **)&dDesc, sizeof(PairDesc) * pairCap, s));
-        CK(cudaMallocAsync((void **)&dState, sizeof(PairState) * pairCap, s));
-        CK(cudaMallocAsync((void **)&dFinished, sizeof(int32_t) * (pairCap + 1), s));
+        CK(malloc_async_retry((void **)&dDesc, sizeof(PairDesc) * pairCap, s));
+        CK(malloc_async_retry((void **)&dState, sizeof(PairState) * pairCap, s));
+        CK(malloc_async_retry((void **)&dFinished, sizeof(int32_t) * (pairCap + 1), s));
         CK(cudaMemsetAsync(dFinished, 0, sizeof(int32_t), s));
         CK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&evSide, cudaEventDisableTiming));
@@ -443,7 +474,7 @@ struct ResidentSet
             else
             {
                 int64_t const b = std::max<int64_t>(sizeInts, 1) * 4;
-                CK(cudaMallocAsync((void **)&rg.ptr, (size_t)b, st));
+                CK(malloc_async_retry((void **)&rg.ptr, (size_t)b, st));
                 owner.push_back(rg.ptr);
                 bytesHeld += b;
                 if (&owner == &keep) keepBytes += b;
@@ -729,6 +760,12 @@ struct ResidentSet
                 pilot->cells += (double)d.la * d.lb;
                 pilot->edges += d.E;
                 pilot->inters += d.D;
+                if (d.bandW > 0)
+                {
+                    pilot->band = true;
+                    int const lo = std::min(d.dMin - ctx.bandMargin, 0), hi = std::max(d.dMax + ctx.bandMargin, 0);
+                    if (d.E > 0 && d.dMin <= d.dMax) pilot->bandSlack = std::max(pilot->bandSlack, hi - lo + 1 - (d.la - d.lb + 1));
+                }
                 // scores + trace + closed-form records of the band, or stream + trace of the full-matrix kernel
                 pilot->dpBytes += d.bandW > 0 ? 4.6 * d.bandW * (d.lb + 1) + 16.0 * (d.la + d.lb + 2)
                                  : (d.dense ? 5.0 * (d.la + 1.0) * (d.lb + 1.0) : 4.0 * d.nVals + 128.0 * d.nSteps * d.W);
@@ -850,7 +887,7 @@ struct ResidentSet
         {
             if (dTable) CK(cudaFreeAsync(dTable, s));
             tableCap = table.size() + table.size() / 4 + 1024;
-            CK(cudaMallocAsync((void **)&dTable, sizeof(int32_t) * tableCap, s));
+            CK(malloc_async_retry((void **)&dTable, sizeof(int32_t) * tableCap, s));
         }
         if (!table.empty())
         {
@@ -976,15 +1013,32 @@ struct ResidentSet
 // sample of the device's pairs (run_device) with a safety factor: bitmap C / 8 + per edge 36 + per interaction 56 + DP
 // arrays + lines, candidates, row starts.  The edge filter's scratch (4 C) is held during the set-up of a cohort only.
 // `scale`: correction of the resident part from the cohorts a worker has admitted so far (run_worker).
+// The DP arrays are estimated per pair, not from a density: the band must hold the diagonals 0 .. la - lb (both corners
+// of the matrix lie on active diagonals) plus what the sample needed beyond them, rounded up to a band width that exists;
+// a mean over all pairs is off by a factor of 8 either way for the longest and the most unequal pairs of C5 (the complete
+// C5 ran out of memory on it).
 double pair_bytes(Device const & dv, OrientedPair const & op, double scale = 1.0)
 {
     double const cells = std::max(dv.pilot.cells, 1.0);
-    double const ePerCell = 1.3 * dv.pilot.edges / cells, dPerCell = 1.3 * dv.pilot.inters / cells, dpPerCell = 1.3 * dv.pilot.dpBytes / cells;
+    double const ePerCell = 1.3 * dv.pilot.edges / cells, dPerCell = 1.3 * dv.pilot.inters / cells;
     double const C = (double)op.la * op.lb;
-    return 4.0 * C + scale * (C / 8 + (36.0 * ePerCell + 56.0 * dPerCell + dpPerCell) * C + 64.0 * (op.la + op.lb) + 4096);
+    double dp = 1.3 * dv.pilot.dpBytes / cells * C;
+    if (dv.pilot.band)
+    {
+        int const need = op.la - op.lb + 1 + dv.pilot.bandSlack;
+        int W = 32;
+        while (W < need) W <<= 1;
+        bool const full = W > 1024 || (op.lb <= 32 * kMaxR && (double)W * (op.lb + 1) >= C);
+        // band: scores + trace + closed-form records, 15 % for the unequal rows and the empty slots of a group;
+        // full matrix: the denser of the two full-matrix forms
+        dp = full ? 5.0 * (op.la + 1.0) * (op.lb + 1.0)
+                  : 1.15 * (4.6 * W * (op.lb + 1.0) + 16.0 * (op.la + op.lb + 2.0));
+    }
+    return 4.0 * C + scale * (C / 8 + (36.0 * ePerCell + 56.0 * dPerCell) * C + dp + 64.0 * (op.la + op.lb) + 4096);
 }
 
-// What one of the device's nWorkers workers may hold: its share of 70 % of the device, but not more than what is free
+// What one of the device's nWorkers workers may hold: its share of 55 % of the device (the stream-ordered pool keeps
+// freed blocks per stream, so the footprint runs ahead of the bytes held; at 70 % the complete C5 met "out of memory"), but not more than what is free
 // now plus the slabs the workers already hold (other contexts or processes may live on the same device).
 double worker_budget(lara_ctx const & ctx, Device & dv, int nWorkers)
 {
@@ -993,7 +1047,7 @@ double worker_budget(lara_ctx const & ctx, Device & dv, int nWorkers)
     cudaMemGetInfo(&freeB, &totalB);
     double held = 0;
     for (Worker const & w : dv.workers) held += 4.0 * (double)w.slabInts;
-    return std::min(0.70 * (double)totalB, 0.9 * ((double)freeB + held)) / (double)nWorkers;
+    return std::min(0.55 * (double)totalB, 0.9 * ((double)freeB + held)) / (double)nWorkers;
 }
 
 size_t batch_limit(lara_ctx & ctx, Device & dv, size_t begin, int nWorkers, double & bytes, double budgetScale = 1.0,
@@ -1065,12 +1119,15 @@ void run_worker(lara_ctx & ctx, Device & dv, Worker & wk, int nWorkers)
                 for (size_t k = b; k < e; ++k) x += pair_bytes(dv, dv.pairs[k]) - 4.0 * (double)dv.pairs[k].la * dv.pairs[k].lb;
                 return x;
             };
-            // after a cohort from the pool: how its bytes compare with the estimate (10 % on top; never above the a-priori one)
+            // after a cohort from the pool: how its bytes compare with the estimate (10 % on top; never below the a-priori one)
             auto calibrate = [&](size_t b, size_t e, int64_t heldBefore)
             {
                 if (e - b < 256) return;
                 double const ratio = (double)(rs.bytesHeld - heldBefore) / std::max(resident_estimate(b, e), 1.0);
-                estScale = std::min(1.0, std::max(0.3, 1.1 * ratio));
+                // one-sided: the queue is sorted by length, and what the longest pairs hold per estimated byte says nothing
+                // about the pairs behind them (complete C5: 0.13 for the first 2,000 pairs, above 1 for the next 15,000, and
+                // "out of memory" when the first figure sized the second cohort); a set that outgrew its estimate does count
+                estScale = std::min(1.5, std::max(1.0, 1.1 * ratio));
                 if (ctx.verbose)
                     std::fprintf(stderr, "[lara_b200] dev %d cohort %zu+%zu: %.2f GB resident, %.2f of the estimate; set holds %.2f of %.2f GB\n",
                                  dv.id, b, e - b, (double)(rs.bytesHeld - heldBefore) / 1e9, ratio, (double)rs.bytesHeld / 1e9, budget / 1e9);

@@ -175,6 +175,8 @@ def test_solve_kernel_variants(built, env, monkeypatch):
     (dict(LARA_B200_MEMBUDGET="6", LARA_B200_WORKERPAIRS="80", LARA_B200_REFILL="2"), 2),       # cohorts limited by the memory budget
     (dict(LARA_B200_MEMBUDGET="4", LARA_B200_WORKERPAIRS="1000", LARA_B200_REFILL="1"), 1),
     (dict(LARA_B200_MEMBUDGET="3", LARA_B200_WORKERPAIRS="1000", LARA_B200_REFILL="0"), 1),
+    # every third pool allocation is told "out of memory" once: drain the device, trim the pool, allocate again
+    (dict(LARA_B200_BATCHCAP="30", LARA_B200_WORKERPAIRS="60", LARA_B200_REFILL="2", LARA_B200_FAILALLOC="3"), 2),
 ])
 def test_solve_many_batches_per_worker(built, env, workers, monkeypatch):
     """Concurrent workers whose resident sets (24..50 slots, or what fits 3..6 MB) are refilled many times from the
