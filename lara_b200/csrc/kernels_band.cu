@@ -48,6 +48,9 @@
 #ifndef LARA_BAND_DPX
 #define LARA_BAND_DPX 0
 #endif
+#ifndef LARA_BAND_INFLOW_SELECT
+#define LARA_BAND_INFLOW_SELECT 0
+#endif
 
 namespace lara
 {
@@ -56,6 +59,13 @@ namespace
 {
 
 constexpr unsigned kFull = 0xffffffffu;
+
+// 16-byte store under a predicate, without a branch
+__device__ __forceinline__ void store_if(bool on, int4 * p, int4 v)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %0, 0;\n\t@q st.global.v4.s32 [%1], {%2, %3, %4, %5};\n\t}"
+                 :: "r"((int)on), "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 
 // One trace unit = the decisions of one run of Q cells as four BIT PLANES of Q bits (plane k = decision bit k of
 // lara_gpu.cuh: kTrGap, kTrFromH, kTrVOpen, kTrHOpen; bit j of a plane = cell j of the run): 2, 4 or 8 bytes.
@@ -243,6 +253,21 @@ band_body(int const warp, int nSlots, int32_t const * __restrict__ pairIdx, Pair
         {
             int32_t hL = __shfl_up_sync(kFull, HB, 1, G);
             int32_t sL = __shfl_up_sync(kFull, SB[Q - 1], 1, G);
+#if LARA_BAND_INFLOW_SELECT
+            {
+                // branch-free form: every lane computes the inflow, lane 0 of the pair takes it, the record is stored under a
+                // predicate (the divergent block and its branches were an eighth of a small launch: profiles/README.md r2m)
+                int const c = r + dLo;
+                bool const on = g == 0 && rowValid && c >= 1 && c - 1 <= la;
+                int32_t const tv = VA[0] + ge, ts = SA[0] + go;
+                int32_t const vl = max(tv, ts);
+                int32_t const hx = (c - 1 >= 1) ? (c + r - 2) * ge + go + runL : kBandNeg;
+                int32_t const sx = max(vl, hx);
+                if (g == 0) { hL = on ? hx : kBandNeg; sL = on ? sx : kBandNeg; }
+                store_if(on, lRec + (size_t)(on ? c - 1 : 0) * PPW, make_int4(tv - r * ge, ts - r * ge, runL, 0));
+                runL = on ? max(runL, vl - r * ge - (c - 1) * ge) : runL;
+            }
+#else
             if (g == 0)
             {
                 // the left neighbour (c-1, r) of the run lies in region L, directly below the boundary cell
@@ -259,6 +284,7 @@ band_body(int const warp, int nSlots, int32_t const * __restrict__ pairIdx, Pair
                     runL = max(runL, vl - r * ge - (c - 1) * ge);
                 }
             }
+#endif
             if (rowValid)
             {
                 uint32_t pl[4];
@@ -281,6 +307,19 @@ band_body(int const warp, int nSlots, int32_t const * __restrict__ pairIdx, Pair
         {
             int32_t sU = __shfl_down_sync(kFull, SA[0], 1, G);
             int32_t vU = __shfl_down_sync(kFull, VA[0], 1, G);
+#if LARA_BAND_INFLOW_SELECT
+            {
+                int const c = r + dLo + W - 1;
+                bool const on = g == G - 1 && live && r >= 1 && r - 1 <= lb && c - 1 <= la;
+                int32_t const th = HB + ge, ts = SB[Q - 1] + go;
+                int32_t const hu = max(th, ts);
+                int32_t const vx = (r - 1 >= 1) ? (c + r - 2) * ge + go + runU : kBandNeg;
+                int32_t const sx = max(vx, hu);
+                if (g == G - 1) { vU = on ? vx : kBandNeg; sU = on ? sx : kBandNeg; }
+                store_if(on, uRec + (size_t)(on ? r - 1 : 0) * PPW, make_int4(th - c * ge, ts - c * ge, runU, 0));
+                runU = on ? max(runU, hu - c * ge - (r - 1) * ge) : runU;
+            }
+#else
             if (g == G - 1)
             {
                 // the upper neighbour (c, r-1) of the run's last cell lies in region U, right of the boundary cell
@@ -297,6 +336,7 @@ band_body(int const warp, int nSlots, int32_t const * __restrict__ pairIdx, Pair
                     runU = max(runU, hu - c * ge - (r - 1) * ge);
                 }
             }
+#endif
             if (rowValid)
             {
                 uint32_t pl[4];
