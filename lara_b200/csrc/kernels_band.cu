@@ -49,8 +49,9 @@
 #define LARA_BAND_DPX 0
 #endif
 #ifndef LARA_BAND_INFLOW_SELECT
-#define LARA_BAND_INFLOW_SELECT 0
+#define LARA_BAND_INFLOW_SELECT 1      /* measured: fill launch of a small set 0.308 -> 0.290 ms, all of C3 unchanged */
 #endif
+
 
 namespace lara
 {
