@@ -1282,8 +1282,11 @@ iterate_post_pair(int const p, PairDesc const * __restrict__ desc, PairState * _
 
 // Warp w of the grid takes slot w of the batch's slot table (pairIdx; nullptr: pair w); empty slots and pairs that
 // have finished return at once.
+#ifndef LARA_POST_MINBLOCKS
+#define LARA_POST_MINBLOCKS 6       /* 6: 80 registers, 24 one-warp blocks per SM.  7 (72 registers, 28 blocks) and 8 (64, 32): measured */
+#endif
 template <bool kTracebackOnly>
-__global__ void __launch_bounds__(128, 6)
+__global__ void __launch_bounds__(128, LARA_POST_MINBLOCKS)
 iterate_post_kernel(int n, int32_t const * __restrict__ pairIdx, PairDesc const * __restrict__ desc, PairState * __restrict__ state,
                     int32_t * __restrict__ arena, DevParams P, PairOutHdr * __restrict__ outHdr,
                     int32_t * __restrict__ outLines, int64_t const * __restrict__ outOff,
