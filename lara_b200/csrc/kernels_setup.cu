@@ -76,6 +76,21 @@ __device__ int32_t filter_sweep(int la, int lb, uint8_t const * __restrict__ A, 
                 }
                 int const ai = kBackward ? la - c : c - 1;
                 int const ca = (int)A[ai];
+                // backward sweep: the forward values of the step's cells are fetched together, before the cell loop (between
+                // the loop's atomics the compiler keeps the loads in program order: one exposed latency per CELL), and the
+                // step's active bits (at most two words of bitmap row a) go out as at most two atomics after it
+                int32_t fw[kBackward ? RF : 1];
+                uint32_t actHi = 0u, actLo = 0u;
+                int const bTop = lb - (rBase + 1);                  // b of the strip's first row; the words bTop >> 5 and the one below
+                if (kBackward)
+                {
+                    #pragma unroll
+                    for (int j = 0; j < RF; ++j)
+                    {
+                        int const b = bTop - j;
+                        fw[j] = (b >= 0) ? fwdP[(size_t)(la - c) * lb + b] : 0;
+                    }
+                }
                 int32_t diag = diagTop;
                 diagTop = max3(uM, uX, uY);
                 #pragma unroll
@@ -92,14 +107,22 @@ __device__ int32_t filter_sweep(int la, int lb, uint8_t const * __restrict__ A, 
                             fwdP[(size_t)(c - 1) * lb + (r - 1)] = diag;
                         else
                         {
-                            int const a = la - c, b = lb - r;
-                            if (fwdP[(size_t)a * lb + b] + sub + diag >= threshold)
-                                atomicOr(&bits[(size_t)a * bitWords + (b >> 5)], 1u << (b & 31));
+                            int const b = lb - r;
+                            if (fw[j] + sub + diag >= threshold)
+                            {
+                                if ((b >> 5) == (bTop >> 5)) actHi |= 1u << (b & 31); else actLo |= 1u << (b & 31);
+                            }
                         }
                     }
                     diag = Pl[j];
                     Ml[j] = m; Xl[j] = x; Yl[j] = y; Pl[j] = max3(m, x, y);
                     uM = m; uX = x; uY = y;
+                }
+                if (kBackward)
+                {
+                    uint32_t * const row = bits + (size_t)(la - c) * bitWords;
+                    if (actHi) atomicOr(row + (bTop >> 5), actHi);
+                    if (actLo) atomicOr(row + (bTop >> 5) - 1, actLo);
                 }
                 botM = uM; botX = uX; botY = uY;
                 if (lane == 31 && pass + 1 < nPass)
