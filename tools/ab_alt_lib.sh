@@ -1,5 +1,6 @@
 #!/bin/bash
-# Developer tool (GPU box): A/B of lara_b200/alt/liblara_b200.so against the library in the tree: parity, 1/8 share, all of C3
+# Developer tool (GPU box): A/B of a second build (lara_b200/alt/liblara_b200.so, made with
+#   BUILD=build_x OUT=../alt EXTRA=-D... bash lara_b200/csrc/build.sh) against the library in the tree: parity, 1/8 share, all of C3
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 ALT=$PWD/lara_b200/alt/liblara_b200.so
