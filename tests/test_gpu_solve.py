@@ -273,3 +273,40 @@ def test_solve_round_trip_property(built):
         assert all(a < b for a, b in zip(lo, lo[1:])) and all(a < b for a, b in zip(hi, hi[1:]))
         assert not lo or (0 <= lo[0] and lo[-1] < 300 and 0 <= hi[0] and hi[-1] < 300)
         assert all(x[2] in (500, 1000) for x in r.lines)
+
+
+@pytest.mark.parametrize("kw", [
+    dict(),
+    dict(balance=0.35, sequence_scale=1.7),
+    dict(balance=1.9, suboptimal_diff=12.5),
+    dict(sequence_scale=0.4, suboptimal_diff=75.0, step_mode=1),
+])
+@pytest.mark.parametrize("fmt", ["ebpseq", "dbn"])
+def test_lagrange_constructor(built, kw, fmt):
+    """Row a4 on its own (Lagrange::Lagrange, src/lagrange.hpp:233-309): after ONE iteration nothing but the edge filter
+    and the constructor has shaped the result.  The number of active edges and of interactions (dual dimension) of every
+    pair set, the first upper bound (Gotoh over the initial queue tops seqScore + max structScore, i.e. every
+    structScore in the reference's float order) and the first lower bound and lines must equal the CPU restatement's, for
+    balance / scale / filter parameters away from their defaults."""
+    import lara_b200 as lb
+    from oracle import binding as ob
+    files = util.make_input(seed=71, n=9, length=60, fmt=fmt, lenmax=170)
+    store = util.load_store(files)
+    p = lb.Parameters()
+    p.set(num_iterations=1, max_nondecreasing=1, **kw)
+    flat = store.flat()
+    ia, ib = ob.all_pairs(len(store))
+    ctx = lb.Context(p)
+    ctx.set_sequences(flat)
+    rg = ctx.solve_pairs(ia, ib)
+    got = lb.results_to_list(rg)
+    st = ctx.stats()
+    ctx.free(rg)
+    ctx.close()
+    ro, so = ob.solve_pairs(p, flat, ia, ib, n_threads=4)
+    want = lb.results_to_list(ro)
+    ob.free_results(ro)
+    assert st.n_active_edges == so.n_active_edges and st.n_active_edges > 0
+    assert st.n_interactions == so.n_interactions and st.n_interactions > 0
+    assert util.results_equal(got, want) is None, util.results_equal(got, want)
+    assert all(r.iterations == 1 for r in got)
