@@ -94,6 +94,10 @@ struct Device
     size_t nextBegin = 0;                   // next unassigned pair of `pairs`
     DevInputs in{};
     void * dSeq = nullptr, * dSeqOff = nullptr, * dBpPartner = nullptr, * dBpWeight = nullptr, * dBpOff = nullptr;
+    // capacities in bytes of the input and output arrays: a call that fits what the call before allocated makes no
+    // cudaMalloc / cudaFree (both take a driver lock that other processes on the box hold for 0.2-0.7 s at times:
+    // profiles/README.md r2v)
+    size_t capSeq = 0, capSeqOff = 0, capBpPartner = 0, capBpWeight = 0, capBpOff = 0, capOutHdr = 0, capOutLines = 0, capOutOff = 0;
     int32_t * negBuf = nullptr;
     std::vector<cudaEvent_t> events;        // two scratch events for copies / microbenchmarks
     cudaEvent_t evRun0 = nullptr, evRun1 = nullptr;     // span of one run_device on the stream
@@ -285,12 +289,25 @@ void device_free_inputs(Device & dv)
 {
     cudaFree(dv.dSeq); cudaFree(dv.dSeqOff); cudaFree(dv.dBpPartner); cudaFree(dv.dBpWeight); cudaFree(dv.dBpOff);
     dv.dSeq = dv.dSeqOff = dv.dBpPartner = dv.dBpWeight = dv.dBpOff = nullptr;
+    dv.capSeq = dv.capSeqOff = dv.capBpPartner = dv.capBpWeight = dv.capBpOff = 0;
 }
 
 void device_free_outputs(Device & dv)
 {
     cudaFree(dv.dOutHdr); cudaFree(dv.dOutLines); cudaFree(dv.dOutOff);
     dv.dOutHdr = nullptr; dv.dOutLines = nullptr; dv.dOutOff = nullptr;
+    dv.capOutHdr = dv.capOutLines = dv.capOutOff = 0;
+}
+
+// device array of at least `bytes`: kept when it is large enough, else freed and allocated anew
+template <typename T>
+void ensure_device(T *& p, size_t & cap, size_t bytes)
+{
+    bytes = std::max<size_t>(bytes, 1);
+    if (p && cap >= bytes) return;
+    if (p) { CK(cudaFree(p)); p = nullptr; cap = 0; }
+    CK(cudaMalloc((void **)&p, bytes));
+    cap = bytes;
 }
 
 double ev_ms(cudaEvent_t a, cudaEvent_t b)
@@ -1629,14 +1646,13 @@ int lara_gpu_set_sequences(lara_ctx * ctx, int32_t n_seq, uint8_t const * seq_ca
         for (Device & dv : ctx->devs)
         {
             CK(cudaSetDevice(dv.id));
-            device_free_inputs(dv);
             cudaEvent_t e0 = dv.events[0], e1 = dv.events[1];
             CK(cudaEventRecord(e0, dv.stream));
-            CK(cudaMalloc(&dv.dSeq, (size_t)std::max<int64_t>(total, 1)));
-            CK(cudaMalloc(&dv.dSeqOff, sizeof(int64_t) * (size_t)(n_seq + 1)));
-            CK(cudaMalloc(&dv.dBpOff, sizeof(int64_t) * (size_t)(total + 1)));
-            CK(cudaMalloc(&dv.dBpPartner, sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1)));
-            CK(cudaMalloc(&dv.dBpWeight, sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1)));
+            ensure_device(dv.dSeq, dv.capSeq, (size_t)std::max<int64_t>(total, 1));
+            ensure_device(dv.dSeqOff, dv.capSeqOff, sizeof(int64_t) * (size_t)(n_seq + 1));
+            ensure_device(dv.dBpOff, dv.capBpOff, sizeof(int64_t) * (size_t)(total + 1));
+            ensure_device(dv.dBpPartner, dv.capBpPartner, sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1));
+            ensure_device(dv.dBpWeight, dv.capBpWeight, sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1));
             CK(cudaMemcpyAsync(dv.dSeq, seq_cat, (size_t)total, cudaMemcpyHostToDevice, dv.stream));
             CK(cudaMemcpyAsync(dv.dSeqOff, seq_off, sizeof(int64_t) * (size_t)(n_seq + 1), cudaMemcpyHostToDevice, dv.stream));
             CK(cudaMemcpyAsync(dv.dBpOff, bp_off, sizeof(int64_t) * (size_t)(total + 1), cudaMemcpyHostToDevice, dv.stream));
@@ -1701,16 +1717,15 @@ int lara_gpu_prepare_pairs(lara_ctx * ctx, int64_t n_pairs, int32_t const * idx_
         {
             Device & dv = ctx->devs[k];
             CK(cudaSetDevice(dv.id));
-            device_free_outputs(dv);
             dv.pairs.clear(); dv.pilot = Pilot{};
             for (size_t q = k; q < all.size(); q += nd) dv.pairs.push_back(all[q]);   // interleaved shares
             dv.outOff.assign(dv.pairs.size() + 1, 0);
             for (size_t q = 0; q < dv.pairs.size(); ++q) dv.outOff[q + 1] = dv.outOff[q] + 3ll * dv.pairs[q].lb;
             dv.outLinesTotal = dv.outOff.back();
             size_t const np = std::max<size_t>(dv.pairs.size(), 1);
-            CK(cudaMalloc((void **)&dv.dOutHdr, sizeof(PairOutHdr) * np));
-            CK(cudaMalloc((void **)&dv.dOutLines, sizeof(int32_t) * (size_t)std::max<int64_t>(dv.outLinesTotal, 1)));
-            CK(cudaMalloc((void **)&dv.dOutOff, sizeof(int64_t) * (np + 1)));
+            ensure_device(dv.dOutHdr, dv.capOutHdr, sizeof(PairOutHdr) * np);
+            ensure_device(dv.dOutLines, dv.capOutLines, sizeof(int32_t) * (size_t)std::max<int64_t>(dv.outLinesTotal, 1));
+            ensure_device(dv.dOutOff, dv.capOutOff, sizeof(int64_t) * (np + 1));
             CK(cudaMemcpy(dv.dOutOff, dv.outOff.data(), sizeof(int64_t) * dv.outOff.size(), cudaMemcpyHostToDevice));
         }
     }

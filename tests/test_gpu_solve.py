@@ -310,3 +310,26 @@ def test_lagrange_constructor(built, kw, fmt):
     assert st.n_interactions == so.n_interactions and st.n_interactions > 0
     assert util.results_equal(got, want) is None, util.results_equal(got, want)
     assert all(r.iterations == 1 for r in got)
+
+
+def test_context_reused_with_other_inputs(built):
+    """One context, three input sets in a row (large, small, large again): the device arrays of the inputs and of the
+    result slots are kept between calls when they are large enough, and every call must still give the oracle's bits."""
+    import lara_b200 as lb
+    from oracle import binding as ob
+    p = lb.Parameters()
+    p.set(num_iterations=30, max_nondecreasing=6)
+    ctx = lb.Context(p)
+    for seed, n, length, lenmax in [(81, 10, 80, 160), (82, 4, 30, 50), (83, 11, 90, 170), (82, 4, 30, 50)]:
+        store = util.load_store(util.make_input(seed=seed, n=n, length=length, lenmax=lenmax))
+        flat = store.flat()
+        ia, ib = ob.all_pairs(len(store))
+        ctx.set_sequences(flat)
+        rg = ctx.solve_pairs(ia, ib)
+        got = lb.results_to_list(rg)
+        ctx.free(rg)
+        ro, _ = ob.solve_pairs(p, flat, ia, ib, n_threads=4)
+        want = lb.results_to_list(ro)
+        ob.free_results(ro)
+        assert util.results_equal(got, want) is None, (seed, util.results_equal(got, want))
+    ctx.close()
