@@ -65,6 +65,9 @@ struct Worker
     std::vector<cudaStream_t> aux;
     std::vector<cudaEvent_t> auxJoin;
     cudaEvent_t evFork = nullptr;
+    // stream and event of the set-up of refill cohorts (made once: creating a stream takes the driver's lock)
+    cudaStream_t side = nullptr;
+    cudaEvent_t evSide = nullptr;
     // slab of the batch arrays: grown between batches only, so that the iteration loop never waits for the allocator
     int32_t * slab = nullptr;
     int64_t slabInts = 0;
@@ -436,8 +439,12 @@ struct ResidentSet
         CK(malloc_async_retry((void **)&dState, sizeof(PairState) * pairCap, s));
         CK(malloc_async_retry((void **)&dFinished, sizeof(int32_t) * (pairCap + 1), s));
         CK(cudaMemsetAsync(dFinished, 0, sizeof(int32_t), s));
-        CK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
-        CK(cudaEventCreateWithFlags(&evSide, cudaEventDisableTiming));
+        if (!wk.side)
+        {
+            CK(cudaStreamCreateWithFlags(&wk.side, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&wk.evSide, cudaEventDisableTiming));
+        }
+        side = wk.side; evSide = wk.evSide;
         arena = wk.slab ? wk.slab : reinterpret_cast<int32_t *>(dDesc);
     }
 
@@ -452,8 +459,6 @@ struct ResidentSet
         if (dFinished) cudaFreeAsync(dFinished, s);
         if (dState) cudaFreeAsync(dState, s);
         if (dDesc) cudaFreeAsync(dDesc, s);
-        if (evSide) cudaEventDestroy(evSide);
-        if (side) cudaStreamDestroy(side);
         cohorts.clear(); keep.clear();
         dTable = nullptr; dFinished = nullptr; dState = nullptr; dDesc = nullptr; side = nullptr; evSide = nullptr;
         cudaGetLastError();
@@ -1591,6 +1596,8 @@ void lara_gpu_destroy(lara_ctx * ctx)
             for (cudaEvent_t ev : wk.events) cudaEventDestroy(ev);
             if (wk.evDone) cudaEventDestroy(wk.evDone);
             if (wk.evFork) cudaEventDestroy(wk.evFork);
+            if (wk.evSide) cudaEventDestroy(wk.evSide);
+            if (wk.side) cudaStreamDestroy(wk.side);
             cudaFree(wk.slab);
             for (cudaEvent_t ev : wk.auxJoin) cudaEventDestroy(ev);
             for (cudaStream_t st : wk.aux) cudaStreamDestroy(st);
